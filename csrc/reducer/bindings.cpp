@@ -1,0 +1,48 @@
+// pybind surface of the native host runtime (module name: distributeddataparallel_b200._C).
+#include "reducer.h"
+
+namespace py = pybind11;
+using b200ddp::Reducer;
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.doc() = "B200 data-parallel engine: native reducer, bucket assignment, parameter verification";
+  m.attr("DEFAULT_FIRST_BUCKET_BYTES") = b200ddp::kDefaultFirstBucketBytes;
+  m.attr("DEFAULT_BUCKET_BYTES_CAP") = b200ddp::kDefaultBucketBytesCap;
+
+  m.def("compute_bucket_assignment_by_size", &b200ddp::compute_bucket_assignment_by_size, py::arg("tensors"),
+        py::arg("size_limits"), py::arg("tensor_indices") = std::vector<int64_t>{},
+        py::call_guard<py::gil_scoped_release>());
+  m.def("pack_param_metadata", &b200ddp::pack_param_metadata);
+  m.def("compare_param_metadata", &b200ddp::compare_param_metadata);
+  m.def("plan_coalesced_groups", &b200ddp::plan_coalesced_groups);
+
+  using release = py::call_guard<py::gil_scoped_release>;
+  py::class_<Reducer, std::shared_ptr<Reducer>>(m, "Reducer")
+      .def(py::init<std::vector<at::Tensor>, std::vector<std::vector<int64_t>>, py::object, py::object, int64_t,
+                    bool, bool, std::vector<std::string>, int64_t, int64_t>(),
+           py::arg("params"), py::arg("bucket_indices"), py::arg("comm"), py::arg("allocator"),
+           py::arg("world_size"), py::arg("gradient_as_bucket_view") = true,
+           py::arg("find_unused_parameters") = false, py::arg("param_names") = std::vector<std::string>{},
+           py::arg("first_bucket_bytes") = b200ddp::kDefaultFirstBucketBytes,
+           py::arg("bucket_bytes_cap") = b200ddp::kDefaultBucketBytesCap)
+      .def("prepare_for_forward", &Reducer::prepare_for_forward, release())
+      .def("prepare_for_backward", &Reducer::prepare_for_backward, release())
+      .def("should_rebuild_buckets", &Reducer::should_rebuild_buckets, release())
+      .def("rebuild_order", &Reducer::rebuild_order)
+      .def("rebuild_buckets", &Reducer::rebuild_buckets, release())
+      .def("set_require_sync", &Reducer::set_require_sync)
+      .def("require_sync", &Reducer::require_sync)
+      .def("set_comm", &Reducer::set_comm)
+      .def("detach_hooks", &Reducer::detach_hooks)
+      .def("num_buckets", &Reducer::num_buckets)
+      .def("bucket_sizes", &Reducer::bucket_sizes)
+      .def("bucket_params", &Reducer::bucket_params)
+      .def("bucket_flat", &Reducer::bucket_flat)
+      .def("grad_slot", &Reducer::grad_slot)
+      .def("logging_data", &Reducer::logging_data)
+      .def("iterations", &Reducer::iterations)
+      .def("has_rebuilt", &Reducer::has_rebuilt)
+      .def("note_graph_replay", &Reducer::note_graph_replay)
+      .def("_autograd_hook", &Reducer::autograd_hook, release())
+      .def("_finalize_backward", &Reducer::finalize_backward, release());
+}

@@ -1,0 +1,106 @@
+"""One training step, eager or replayed from a CUDA graph.
+
+The reference's step is seven Python statements (/root/reference/dpp.py:48-53) that expand
+into ~300 kernel launches for 7 GFLOP of math ("the stock stack is
+launch-/latency-bound on B200").  ``TrainStep`` keeps the same semantics
+
+    optimizer.zero_grad(); out = model(x); loss = criterion(out, y); loss.backward(); optimizer.step()
+
+but, once bucket layout and shapes are final (after the one-time bucket rebuild of
+iteration 1), captures the *whole* step -- forward, backward, the reducer's overlapped
+bucket all-reduces on the side stream, and the fused optimizer update -- into one CUDA
+graph and replays it.  Hooks run at capture time only; what is replayed is the kernel
+DAG they produced, including the fork/join onto the communication stream.
+
+A batch whose shape differs from the captured one (the ragged last batch of an epoch,
+SURVEY §3.4) runs eagerly.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+
+class TrainStep:
+    def __init__(self, model: nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
+                 cuda_graph: bool = True, warmup_steps: int = 3) -> None:
+        self.model = model
+        self.criterion = criterion
+        self.optimizer = optimizer
+        self.warmup_steps = max(3, int(warmup_steps))
+        self.steps = 0
+        self.replays = 0
+        self.eager_steps = 0
+        self._graphs: Dict[Tuple, dict] = {}
+        dev = next(model.parameters()).device
+        self.use_graph = bool(cuda_graph) and dev.type == "cuda"
+        self._ddp = model if hasattr(model, "reducer") else None
+
+    # -- eager ---------------------------------------------------------------------------
+    def _eager(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        self.optimizer.zero_grad()
+        out = self.model(data)
+        loss = self.criterion(out, target)
+        loss.backward()
+        self.optimizer.step()
+        self.eager_steps += 1
+        return loss.detach()
+
+    # -- graph ---------------------------------------------------------------------------
+    def _ready_for_capture(self) -> bool:
+        if self.steps < self.warmup_steps:
+            return False
+        if self._ddp is not None and not self._ddp.find_unused_parameters:
+            return bool(self._ddp.reducer.has_rebuilt())
+        return True
+
+    def _capture(self, data: torch.Tensor, target: torch.Tensor) -> dict:
+        static_x = data.clone(memory_format=torch.preserve_format)
+        static_y = target.clone()
+        self.optimizer.zero_grad(set_to_none=True)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = self.model(static_x)
+            loss = self.criterion(out, static_y)
+            loss.backward()
+            self.optimizer.step()
+        entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach(), "out": out.detach()}
+        return entry
+
+    def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        self.steps += 1
+        if not self.use_graph or not self.model.training:
+            return self._eager(data, target)
+        key = (tuple(data.shape), data.dtype, tuple(target.shape))
+        entry = self._graphs.get(key)
+        if entry is None:
+            if not self._ready_for_capture() or len(self._graphs) >= 1:
+                # only the steady-state shape is captured; other shapes (ragged tail) stay eager
+                return self._eager(data, target)
+            entry = self._graphs[key] = self._capture(data, target)
+            # the capture itself does not execute the step: fall through to a replay
+        entry["x"].copy_(data, non_blocking=True)
+        entry["y"].copy_(target, non_blocking=True)
+        entry["graph"].replay()
+        self.replays += 1
+        if self._ddp is not None:
+            self._ddp.reducer.note_graph_replay()
+        return entry["loss"]
+
+    def load_inputs_and_replay(self, entry_key=None) -> torch.Tensor:
+        """Replay on whatever is already in the static input buffers (bench helper)."""
+        entry = next(iter(self._graphs.values())) if entry_key is None else self._graphs[entry_key]
+        entry["graph"].replay()
+        self.replays += 1
+        return entry["loss"]
+
+    @property
+    def captured(self) -> bool:
+        return bool(self._graphs)
+
+    def static_inputs(self):
+        entry = next(iter(self._graphs.values()))
+        return entry["x"], entry["y"]

@@ -1,0 +1,120 @@
+"""The per-rank training program.
+
+``train(rank, world_size, epochs=5)`` has the reference's name, signature and loop
+structure (/root/reference/dpp.py:27-57): setup -> seed 0 -> CIFAR-10 + rank-sharded
+sampler + batch 32 -> SimpleCNN -> DDP -> CrossEntropy + SGD(lr=0.01) -> epoch loop with
+``sampler.set_epoch`` -> rank-0 print of the local loss every 100 batches (same text) ->
+cleanup.  The optional ``cfg`` widens it (backend, synthetic data, checkpointing, graphs).
+"""
+from __future__ import annotations
+
+import time
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from . import ops
+from .checkpoint import load_checkpoint, save_checkpoint
+from .config import TrainConfig
+from .data import DeviceLoader, SyntheticTokens, cifar10
+from .engine import TrainStep
+from .launch import cleanup, setup
+from .optim import SGD, Adam
+from .parallel.ddp import DistributedDataParallel as DDP
+from .sampler import DistributedSampler
+
+
+class CrossEntropyLoss(nn.Module):
+    """Mean-reduced softmax cross entropy (dpp.py:40), one fused fwd+bwd kernel on CUDA."""
+
+    def forward(self, logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        return ops.cross_entropy(logits, target)
+
+
+def build_model(cfg: TrainConfig) -> nn.Module:
+    from . import models
+
+    name = cfg.model.lower()
+    if name in ("simplecnn", "dpp", "resnet18-cifar"):
+        return models.SimpleCNN(cfg.num_classes, pretrained=cfg.pretrained)
+    if name == "resnet18":
+        return models.resnet18(cfg.num_classes)
+    if name == "resnet50":
+        return models.resnet50(cfg.num_classes)
+    if name.startswith("gpt2"):
+        return models.gpt2(name, seq_len=cfg.seq_len)
+    raise ValueError(f"unknown model {cfg.model!r}")
+
+
+def build_optimizer(cfg: TrainConfig, params):
+    if cfg.optimizer == "adam":
+        return Adam(params, lr=cfg.lr, weight_decay=cfg.weight_decay)
+    return SGD(params, lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay)   # dpp.py:41
+
+
+def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig] = None) -> dict:
+    cfg = cfg or TrainConfig()
+    device_type = cfg.resolved_device()
+    setup(rank, world_size, backend=cfg.resolved_backend(), master_addr=cfg.master_addr,
+          master_port=cfg.master_port)                                      # dpp.py:28
+    torch.manual_seed(cfg.seed)                                             # dpp.py:29
+    device = torch.device("cuda", rank % torch.cuda.device_count()) if device_type == "cuda" else torch.device("cpu")
+    ops.set_native(cfg.native_ops)
+
+    dataset = cifar10(cfg.data_root, train=True, synthetic=cfg.synthetic, n=cfg.dataset_size, rank=rank)   # :33
+    sampler = DistributedSampler(dataset, num_replicas=world_size, rank=rank, shuffle=True)               # :34
+    if hasattr(dataset, "data"):
+        dataloader = DeviceLoader(dataset, cfg.batch_size, sampler, device)                               # :35
+    else:
+        from torch.utils.data import DataLoader
+
+        dataloader = DataLoader(dataset, batch_size=cfg.batch_size, sampler=sampler)
+
+    model = build_model(cfg).to(device)                                     # dpp.py:38
+    model = DDP(model, device_ids=[device.index] if device.type == "cuda" else None,
+                broadcast_buffers=cfg.broadcast_buffers, bucket_cap_mb=cfg.bucket_cap_mb,
+                first_bucket_mb=cfg.first_bucket_mb, comm=cfg.comm, allreduce_algo=cfg.allreduce_algo)   # :39
+    criterion = CrossEntropyLoss()                                          # dpp.py:40
+    optimizer = build_optimizer(cfg, model.parameters())                    # dpp.py:41
+
+    start_epoch, global_step = 0, 0
+    if cfg.resume:
+        info = load_checkpoint(cfg.resume, model, optimizer, sampler, map_location=device)
+        start_epoch, global_step = info["epoch"], info["step"]
+
+    step_fn = TrainStep(model, criterion, optimizer, cuda_graph=cfg.cuda_graph)
+    history = []
+    t0 = time.time()
+    seen = 0
+    done = False
+    for epoch in range(start_epoch, epochs):                                # dpp.py:44
+        model.train()                                                       # dpp.py:45
+        sampler.set_epoch(epoch)                                            # dpp.py:46
+        for batch_idx, (data, target) in enumerate(dataloader):             # dpp.py:47
+            if data.device != device:
+                data, target = data.to(device), target.to(device)           # dpp.py:48
+            loss = step_fn(data, target)                                    # dpp.py:49-53
+            global_step += 1
+            seen += data.shape[0]
+            if batch_idx % cfg.log_interval == 0 and rank == 0:             # dpp.py:54-55
+                val = loss.item()
+                history.append(val)
+                line = f"Epoch {epoch}, Batch {batch_idx}, Loss: {val}"
+                if cfg.print_throughput:
+                    line += f"  [{seen * world_size / max(time.time() - t0, 1e-9):.0f} samples/s]"
+                print(line, flush=True)
+            if cfg.max_steps is not None and global_step >= cfg.max_steps:
+                done = True
+                break
+        if cfg.checkpoint_path and (done or epoch == epochs - 1 or
+                                    (cfg.checkpoint_every and (epoch + 1) % cfg.checkpoint_every == 0)):
+            save_checkpoint(cfg.checkpoint_path, model, optimizer, epoch=epoch + 1, step=global_step, sampler=sampler)
+        if done:
+            break
+    stats = {"steps": global_step, "loss_history": history, "graph_replays": step_fn.replays,
+             "ddp": model._get_ddp_logging_data()}
+    del step_fn
+    cleanup()                                                               # dpp.py:57
+    return stats

@@ -1,0 +1,69 @@
+"""Bucket assignment parity with dist._compute_bucket_assignment_by_size."""
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+
+import distributeddataparallel_b200 as d
+from distributeddataparallel_b200 import _C
+
+MiB = 1 << 20
+
+
+def _params(model):
+    return [p for p in model.parameters() if p.requires_grad]
+
+
+def test_resnet18_steady_state_buckets():
+    ps = _params(d.SimpleCNN())
+    assert len(ps) == 62 and sum(p.numel() * 4 for p in ps) == 44_726_568
+    rev = list(reversed(ps))
+    idx = list(reversed(range(len(ps))))
+    buckets, limits = _C.compute_bucket_assignment_by_size(rev, [MiB, 25 * MiB], idx)
+    sizes = [sum(ps[i].numel() * 4 for i in b) for b in buckets]
+    assert [len(b) for b in buckets] == [5, 15, 42]
+    assert sizes == [9_461_800, 26_494_976, 8_769_792]
+    ref, ref_limits = dist._compute_bucket_assignment_by_size(rev, [MiB, 25 * MiB], [False] * len(rev), idx)
+    assert buckets == ref and limits == ref_limits
+
+
+def test_first_iteration_single_bucket():
+    ps = _params(d.SimpleCNN())
+    buckets, _ = _C.compute_bucket_assignment_by_size(ps, [sys.maxsize])
+    assert len(buckets) == 1 and len(buckets[0]) == 62
+
+
+@pytest.mark.parametrize("dtype,expect", [(torch.float32, 5), (torch.bfloat16, 3)])
+def test_resnet50_bucket_counts(dtype, expect):
+    ps = [p.detach().to(dtype) for p in _params(d.resnet50())]
+    rev = list(reversed(ps))
+    idx = list(reversed(range(len(ps))))
+    buckets, _ = _C.compute_bucket_assignment_by_size(rev, [MiB, 25 * MiB], idx)
+    ref, _ = dist._compute_bucket_assignment_by_size(rev, [MiB, 25 * MiB], [False] * len(rev), idx)
+    assert buckets == ref and len(buckets) == expect
+
+
+def test_mixed_dtype_and_sorting_parity():
+    g = torch.Generator().manual_seed(0)
+    ts = []
+    for i in range(40):
+        n = int(torch.randint(1, 300_000, (1,), generator=g))
+        ts.append(torch.empty(n, dtype=[torch.float32, torch.float16, torch.float64][i % 3]))
+    for limits in ([MiB], [100_000, MiB], [1, 2 * MiB, 3 * MiB]):
+        mine = _C.compute_bucket_assignment_by_size(ts, limits)
+        ref = dist._compute_bucket_assignment_by_size(ts, limits, [False] * len(ts))
+        assert mine[0] == ref[0] and mine[1] == ref[1]
+
+
+def test_coalesced_group_plan():
+    ts = [torch.empty(10), torch.empty(5, dtype=torch.int64), torch.empty(10), torch.empty(100)]
+    groups = _C.plan_coalesced_groups(ts, 100)
+    assert groups == [[0, 2], [1], [3]]
+
+
+def test_param_metadata_compare():
+    a = _C.pack_param_metadata([torch.empty(2, 3), torch.empty(4)])
+    b = _C.pack_param_metadata([torch.empty(2, 3), torch.empty(5)])
+    assert _C.compare_param_metadata(a, a.clone(), 1) == ""
+    assert "size of dim 0" in _C.compare_param_metadata(a, b, 1)

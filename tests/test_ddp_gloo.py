@@ -1,0 +1,78 @@
+"""Distributed tier on CPU (gloo, world_size 2, mp.spawn): BASELINE.json config #1."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+import _workers as W
+
+
+def _port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_parity_with_stock_ddp(tmp_path, channels_last):
+    ws, steps = 2, 3
+    mp.spawn(W.ddp_parity_worker, args=(ws, _port(), str(tmp_path), steps, channels_last), nprocs=ws, join=True)
+    recs = [torch.load(tmp_path / f"rank{r}.pt") for r in range(ws)]
+    for r in recs:
+        assert r["ctor_equal"], "constructor broadcast must equalise parameters"
+        assert all(r["grads_identical"]), "averaged gradients must be bitwise identical on every rank"
+        if channels_last:
+            # NHWC and NCHW CPU conv kernels round differently and batch-8 BatchNorm on 1x1 maps
+            # amplifies that chaotically after a few updates: only the first step is comparable.
+            assert r["grad_err"][0] < 1e-3 and abs(r["loss_a"][0] - r["loss_b"][0]) < 1e-4
+        else:
+            assert max(r["grad_err"]) < 2e-3
+            for a, b in zip(r["loss_a"], r["loss_b"]):
+                assert abs(a - b) < 1e-3 * max(1.0, abs(b))
+            assert r["param_err"] < 1e-4
+        # iteration 0: one bucket; after the one-time rebuild: three
+        assert r["buckets"] == [1, 3, 3]
+        log = r["log"]
+        assert log["has_rebuilt_buckets"] and log["num_parameter_tensors"] == 62
+        assert log["total_parameter_size_bytes"] == 44_726_568
+        assert log["initial_bucket_sizes"] == [44_726_568]
+        assert log["rebuilt_bucket_sizes"] == [9_461_800, 26_494_976, 8_769_792]
+        assert len(r["keys"]) == 122 and all(k.startswith("module.model.") for k in r["keys"])
+        assert r["keys"][0] == "module.model.conv1.weight" and r["keys"][-1] == "module.model.fc.bias"
+
+
+def test_ddp_features(tmp_path):
+    ws = 2
+    mp.spawn(W.features_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    for r in range(ws):
+        rec = torch.load(tmp_path / f"rank{r}.pt")
+        assert rec["nosync_launches"] >= 1 and rec["nosync_err"] < 1e-5
+        assert rec["hook_identical"] and "compress" in rec["hook_name"]
+        assert rec["unused_grad_zero"] and rec["unused_identical"]
+        assert "find_unused_parameters" in rec["unfinished_error"]
+        assert "same model across all ranks" in rec["mismatch_error"]
+
+
+def test_train_and_resume(tmp_path):
+    ws = 2
+    ckpt = str(tmp_path / "ck.pt")
+    mp.spawn(W.train_worker, args=(ws, _port(), str(tmp_path), ckpt, None), nprocs=ws, join=True)
+    s0 = torch.load(tmp_path / "train0.pt")
+    assert s0["steps"] == 6 and len(s0["loss_history"]) == 3
+    assert os.path.exists(ckpt)
+    payload = torch.load(ckpt, weights_only=False)
+    assert len(payload["model"]) == 122 and payload["step"] == 6
+    assert payload["optimizer"]["param_groups"][0]["lr"] == 0.01
+    assert payload["optimizer"]["param_groups"][0]["params"] == list(range(62))
+    mp.spawn(W.train_worker, args=(ws, _port(), str(tmp_path), ckpt, ckpt), nprocs=ws, join=True)
+    s1 = torch.load(tmp_path / "train0.pt")
+    assert s1["steps"] >= 7
+
+
+def test_fault_injection_fail_fast():
+    ws = 2
+    with pytest.raises(Exception) as ei:
+        mp.spawn(W.failing_worker, args=(ws, _port()), nprocs=ws, join=True)
+    assert "injected failure on rank 1" in str(ei.value)

@@ -1,0 +1,66 @@
+"""Module-tree / state_dict parity with the reference model."""
+import pytest
+import torch
+
+import distributeddataparallel_b200 as d
+
+tv = pytest.importorskip("torchvision")
+
+
+def _stock_simplecnn():
+    class SimpleCNN(torch.nn.Module):          # /root/reference/dpp.py:11-18 with weights=None
+        def __init__(self):
+            super().__init__()
+            self.model = tv.models.resnet18(weights=None)
+            self.model.fc = torch.nn.Linear(512, 10)
+
+        def forward(self, x):
+            return self.model(x)
+
+    return SimpleCNN()
+
+
+def test_state_dict_contract():
+    ours, stock = d.SimpleCNN(), _stock_simplecnn()
+    a, b = ours.state_dict(), stock.state_dict()
+    assert list(a.keys()) == list(b.keys()) and len(a) == 122
+    for k in a:
+        assert a[k].shape == b[k].shape and a[k].dtype == b[k].dtype, k
+    assert sum(v.dtype == torch.int64 for v in a.values()) == 20
+    assert sum(p.numel() for p in ours.parameters()) == 11_181_642
+    assert [n for n, _ in ours.named_parameters()] == [n for n, _ in stock.named_parameters()]
+
+
+def test_seeded_init_matches_stock():
+    torch.manual_seed(0)
+    ours = d.SimpleCNN()
+    torch.manual_seed(0)
+    stock = _stock_simplecnn()
+    for (k, a), (_, b) in zip(ours.state_dict().items(), stock.state_dict().items()):
+        assert torch.equal(a, b), k
+
+
+@pytest.mark.parametrize("batch", [32, 10])
+def test_forward_backward_matches_stock_cpu(batch):
+    torch.manual_seed(0)
+    ours, stock = d.SimpleCNN(), _stock_simplecnn()
+    stock.load_state_dict(ours.state_dict())
+    x = torch.randn(batch, 3, 32, 32)
+    y = torch.randint(0, 10, (batch,))
+    la = d.CrossEntropyLoss()(ours(x), y)
+    lb = torch.nn.functional.cross_entropy(stock(x), y)
+    assert torch.allclose(la, lb, rtol=1e-5, atol=1e-6)
+    la.backward()
+    lb.backward()
+    for (n, p), (_, q) in zip(ours.named_parameters(), stock.named_parameters()):
+        err = (p.grad - q.grad).norm() / q.grad.norm().clamp_min(1e-12)
+        assert err < 2e-3, (n, float(err))
+    for (n, p), (_, q) in zip(ours.named_buffers(), stock.named_buffers()):
+        assert torch.allclose(p.float(), q.float(), rtol=1e-5, atol=1e-6), n
+
+
+def test_resnet50_keys():
+    a = d.resnet50().state_dict()
+    b = tv.models.resnet50(weights=None).state_dict()
+    assert list(a.keys()) == list(b.keys())
+    assert all(a[k].shape == b[k].shape for k in a)
