@@ -1,0 +1,90 @@
+// Small elementwise kernels: input pipeline, scaling, accumulation.
+#include "common.cuh"
+#include "b200ddp.h"
+
+namespace b200 {
+
+// uint8 NHWC -> fp32 NHWC with torchvision's ToTensor + Normalize(mean, std) arithmetic
+// (/root/reference/dpp.py:32): (x / 255 - mean) / std, same operation order, so values match
+// the reference's host-side transform bit for bit.
+__global__ void __launch_bounds__(256) preprocess_u8_kernel(const uint8_t* __restrict__ in, float* __restrict__ out,
+                                                            size_t n, float mean, float stdv) {
+  const size_t n4 = n / 4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const uchar4 u = reinterpret_cast<const uchar4*>(in)[i];
+    float4 o;
+    o.x = __fdiv_rn(__fdiv_rn((float)u.x, 255.f) - mean, stdv);
+    o.y = __fdiv_rn(__fdiv_rn((float)u.y, 255.f) - mean, stdv);
+    o.z = __fdiv_rn(__fdiv_rn((float)u.z, 255.f) - mean, stdv);
+    o.w = __fdiv_rn(__fdiv_rn((float)u.w, 255.f) - mean, stdv);
+    reinterpret_cast<float4*>(out)[i] = o;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const size_t i = n4 * 4 + threadIdx.x;
+    out[i] = __fdiv_rn(__fdiv_rn((float)in[i], 255.f) - mean, stdv);
+  }
+}
+
+// out = a * (*scale_dev or scale_host)
+__global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ a, float* __restrict__ out, size_t n,
+                                                    const float* __restrict__ scale_dev, float scale_host) {
+  const float s = scale_dev ? __ldg(scale_dev) * scale_host : scale_host;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = a[i] * s;
+}
+
+// out = a + b
+__global__ void __launch_bounds__(256) add_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                  float* __restrict__ out, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = a[i] + b[i];
+}
+
+// column sums of a [M, N] matrix (bias gradients): out[n] (+)= sum_m a[m, n]
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ a, float* __restrict__ out, int M, int N,
+                                                     int accumulate) {
+  const int n = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int r0 = threadIdx.x >> 5;   // 8 row lanes
+  __shared__ float sh[8][33];
+  float s = 0.f;
+  if (n < N)
+    for (int m = r0; m < M; m += 8) s += __ldg(a + (size_t)m * N + n);
+  sh[r0][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (r0 == 0 && n < N) {
+    float tot = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) tot += sh[r][threadIdx.x & 31];
+    out[n] = accumulate ? out[n] + tot : tot;
+  }
+}
+
+static int grid1d(size_t n, int per_thread = 4) {
+  size_t g = (n + 256 * per_thread - 1) / (256 * per_thread);
+  return (int)(g < 1 ? 1 : (g > 8 * kNumSMs ? 8 * kNumSMs : g));
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+B200_API int b200_preprocess_u8(const uint8_t* in, float* out, size_t n, float mean, float stdv, cudaStream_t stream) {
+  preprocess_u8_kernel<<<grid1d(n / 4 + 1, 2), 256, 0, stream>>>(in, out, n, mean, stdv);
+  B200_LAUNCH_CHECK();
+}
+
+B200_API int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, float scale_host,
+                        cudaStream_t stream) {
+  scale_kernel<<<grid1d(n), 256, 0, stream>>>(a, out, n, scale_dev, scale_host);
+  B200_LAUNCH_CHECK();
+}
+
+B200_API int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream) {
+  add_kernel<<<grid1d(n), 256, 0, stream>>>(a, b, out, n);
+  B200_LAUNCH_CHECK();
+}
+
+B200_API int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream) {
+  colsum_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(a, out, M, N, accumulate);
+  B200_LAUNCH_CHECK();
+}

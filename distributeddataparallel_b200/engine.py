@@ -61,12 +61,16 @@ class TrainStep:
         static_y = target.clone()
         self.optimizer.zero_grad(set_to_none=True)
         torch.cuda.synchronize()
+        from .ops import native
+
+        launches0 = native.launch_count()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             out = self.model(static_x)
             loss = self.criterion(out, static_y)
             loss.backward()
             self.optimizer.step()
+        native.set_launches_per_capture(native.launch_count() - launches0)
         entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach(), "out": out.detach()}
         return entry
 

@@ -40,13 +40,29 @@ class BatchNorm2d(nn.BatchNorm2d):
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None,
                 relu: bool = False) -> torch.Tensor:
         training = self.training or not self.track_running_stats
+        ws = None
+        if ops.use_native(x):
+            from ..ops import native
+
+            ws = native.bn_workspace(self, self.num_features, x.device)
         return ops.batch_norm_act(
             x, self.weight, self.bias,
             self.running_mean if self.track_running_stats else None,
             self.running_var if self.track_running_stats else None,
             self.num_batches_tracked if (self.training and self.track_running_stats) else None,
             residual=residual, relu=relu, training=training,
-            momentum=0.1 if self.momentum is None else self.momentum, eps=self.eps)
+            momentum=0.1 if self.momentum is None else self.momentum, eps=self.eps, ws=ws)
+
+
+def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Optional[torch.Tensor] = None,
+            relu: bool = False) -> torch.Tensor:
+    """conv -> BN (+residual) (+ReLU).  On the native path this is two launches: the conv's
+    epilogue already accumulates the per-channel statistics BN needs."""
+    if ops.use_native(x) and conv.bias is None and conv.groups == 1 and conv.dilation == (1, 1):
+        from ..ops import native
+
+        return native.conv_bn_act(x, conv.weight, conv.stride[0], conv.padding[0], bn, residual, relu)
+    return bn(conv(x), residual=residual, relu=relu)
 
 
 class Linear(nn.Linear):
@@ -76,11 +92,11 @@ class BasicBlock(nn.Module):
         self.stride = stride
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        out = self.bn1(self.conv1(x), relu=True)
+        out = conv_bn(self.conv1, self.bn1, x, relu=True)
         identity = x
         if self.downsample is not None:
-            identity = self.downsample[1](self.downsample[0](x))
-        return self.bn2(self.conv2(out), residual=identity, relu=True)
+            identity = conv_bn(self.downsample[0], self.downsample[1], x)
+        return conv_bn(self.conv2, self.bn2, out, residual=identity, relu=True)
 
 
 class Bottleneck(nn.Module):
@@ -99,12 +115,12 @@ class Bottleneck(nn.Module):
         self.stride = stride
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        out = self.bn1(self.conv1(x), relu=True)
-        out = self.bn2(self.conv2(out), relu=True)
+        out = conv_bn(self.conv1, self.bn1, x, relu=True)
+        out = conv_bn(self.conv2, self.bn2, out, relu=True)
         identity = x
         if self.downsample is not None:
-            identity = self.downsample[1](self.downsample[0](x))
-        return self.bn3(self.conv3(out), residual=identity, relu=True)
+            identity = conv_bn(self.downsample[0], self.downsample[1], x)
+        return conv_bn(self.conv3, self.bn3, out, residual=identity, relu=True)
 
 
 class ResNet(nn.Module):
@@ -142,7 +158,7 @@ class ResNet(nn.Module):
         return nn.Sequential(*seq)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.bn1(self.conv1(x), relu=True)
+        x = conv_bn(self.conv1, self.bn1, x, relu=True)
         x = ops.max_pool2d(x, 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = ops.global_avg_pool(x)              # avgpool + flatten in one op

@@ -70,11 +70,11 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, stride: int, padding: int,
 
 
 def batch_norm_act(x, weight, bias, running_mean, running_var, num_batches_tracked,
-                   residual=None, relu=False, training=True, momentum=0.1, eps=1e-5):
+                   residual=None, relu=False, training=True, momentum=0.1, eps=1e-5, ws=None):
     """BatchNorm2d (+ residual add) (+ ReLU) as one op; updates running stats in training."""
     if use_native(x):
         return _nat().batch_norm_act(x, weight, bias, running_mean, running_var, num_batches_tracked,
-                                     residual, relu, training, momentum, eps)
+                                     residual, relu, training, momentum, eps, ws)
     if training and num_batches_tracked is not None:
         num_batches_tracked.add_(1)
     y = F.batch_norm(x, running_mean, running_var, weight, bias, training, momentum, eps)

@@ -1,0 +1,487 @@
+"""Bindings + autograd Functions for the sm_100a kernel library (``libb200ddp_kernels.so``).
+
+The library exports a plain C ABI (``include/b200ddp.h``); it is loaded with ctypes and
+driven with raw device pointers on the current torch CUDA stream, so every launch is
+capturable in a CUDA graph.  If the library is missing on a GPU machine it is built in-tree
+with nvcc (sm_100a); failure to load is an error, never a silent fallback.
+
+Gradient placement: a parameter wrapped by our ``DistributedDataParallel`` carries
+``param._grad_slot`` -- its strided view inside the flat gradient bucket.  Weight-gradient
+kernels write **directly into that slot** and return it as the gradient, so autograd's
+``AccumulateGrad`` adopts the slot as ``.grad`` without a copy and the reducer finds the
+gradient already in place (SURVEY.md K18/K19 eliminated).
+"""
+from __future__ import annotations
+
+import ctypes
+import struct
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+_lib = None
+_launches = 0
+_launches_per_capture = 0
+
+
+# ---------------------------------------------------------------------------------------
+# library loading
+# ---------------------------------------------------------------------------------------
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    from .. import _build
+
+    path = _build.build_kernels()
+    lib = ctypes.CDLL(str(path))
+    for name in ("b200_optim_chunk_elems", "b200_optim_rec_bytes"):
+        getattr(lib, name).restype = ctypes.c_int
+    _lib = lib
+    return lib
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def launches_per_capture() -> int:
+    return _launches_per_capture
+
+
+def set_launches_per_capture(n: int) -> None:
+    global _launches_per_capture
+    _launches_per_capture = int(n)
+
+
+def _call(name: str, *args, kernels: int = 1) -> None:
+    global _launches
+    lib = load_library()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed: CUDA error {rc} ({torch.cuda.get_device_name()})")
+    _launches += kernels
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_i = ctypes.c_int
+_f = ctypes.c_float
+_sz = ctypes.c_size_t
+
+
+# ---------------------------------------------------------------------------------------
+# per-device scratch (split-K workspace + tile tickets)
+# ---------------------------------------------------------------------------------------
+class _Scratch:
+    WORKSPACE_BYTES = 32 << 20
+    MAX_COUNTERS = 8192
+
+    def __init__(self, device: torch.device) -> None:
+        self.workspace = torch.empty(self.WORKSPACE_BYTES // 4, dtype=torch.float32, device=device)
+        self.counters = torch.zeros(self.MAX_COUNTERS, dtype=torch.int32, device=device)
+        self.row_loss = torch.empty(1 << 16, dtype=torch.float32, device=device)
+
+
+_scratch: Dict[int, _Scratch] = {}
+
+
+def scratch(device: torch.device) -> _Scratch:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    s = _scratch.get(idx)
+    if s is None:
+        s = _scratch[idx] = _Scratch(torch.device("cuda", idx))
+    return s
+
+
+def _ws_args(dev: torch.device):
+    s = scratch(dev)
+    return (_ptr(s.workspace), _sz(s.WORKSPACE_BYTES), _ptr(s.counters), _i(s.MAX_COUNTERS))
+
+
+# ---------------------------------------------------------------------------------------
+# layout helpers
+# ---------------------------------------------------------------------------------------
+def _nhwc(x: torch.Tensor) -> torch.Tensor:
+    """4-D tensor, logical NCHW, physically dense NHWC, fp32."""
+    if x.dtype != torch.float32:
+        x = x.float()
+    return x.contiguous(memory_format=torch.channels_last)
+
+
+def _empty_nhwc(n, c, h, w, device) -> torch.Tensor:
+    return torch.empty((n, c, h, w), dtype=torch.float32, device=device, memory_format=torch.channels_last)
+
+
+def _grad_target(param: torch.Tensor, slot: Optional[torch.Tensor], like: torch.Tensor):
+    """(tensor to write the gradient into, accumulate?)  Prefer the DDP bucket slot."""
+    if slot is not None and param.grad is None and slot.shape == like.shape:
+        return slot.detach(), False          # fresh alias of the slot: AccumulateGrad adopts it
+    return torch.empty_like(like, memory_format=torch.preserve_format), False
+
+
+# ---------------------------------------------------------------------------------------
+# input pipeline
+# ---------------------------------------------------------------------------------------
+def preprocess_u8(x_u8: torch.Tensor, mean: float = 0.5, std: float = 0.5) -> torch.Tensor:
+    assert x_u8.dtype == torch.uint8 and x_u8.dim() == 4, "expected uint8 [N,H,W,C]"
+    x_u8 = x_u8.contiguous()
+    n, h, w, c = x_u8.shape
+    out = torch.empty((n, h, w, c), dtype=torch.float32, device=x_u8.device)
+    _call("b200_preprocess_u8", _ptr(x_u8), _ptr(out), _sz(x_u8.numel()), _f(mean), _f(std), _stream())
+    return out.permute(0, 3, 1, 2)       # logical NCHW view of NHWC storage (== channels_last)
+
+
+# ---------------------------------------------------------------------------------------
+# convolution
+# ---------------------------------------------------------------------------------------
+def _conv_geom(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int):
+    n, c, h, wd = x.shape
+    k, c2, r, s = w.shape
+    assert c == c2, f"channel mismatch {c} vs {c2}"
+    p = (h + 2 * pad - r) // stride + 1
+    q = (wd + 2 * pad - s) // stride + 1
+    return n, h, wd, c, k, r, s, p, q
+
+
+class _Conv2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, stride, pad, stats):
+        xc, wc = _nhwc(x), _nhwc(w)
+        n, h, wd, c, k, r, s, p, q = _conv_geom(xc, wc, stride, pad)
+        y = _empty_nhwc(n, k, p, q, x.device)
+        _call("b200_conv2d_fprop", _ptr(xc), _ptr(wc), _ptr(None), _ptr(y), _ptr(stats),
+              _i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad), *_ws_args(x.device), _stream())
+        ctx.save_for_backward(xc, wc)
+        ctx.geom = (n, h, wd, c, k, r, s, stride, pad)
+        ctx.param = w
+        ctx.slot = getattr(w, "_grad_slot", None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, wc = ctx.saved_tensors
+        n, h, wd, c, k, r, s, stride, pad = ctx.geom
+        dy = _nhwc(dy)
+        geom = (_i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad))
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = _empty_nhwc(n, c, h, wd, dy.device)
+            _call("b200_conv2d_dgrad", _ptr(dy), _ptr(wc), _ptr(dx), *geom, *_ws_args(dy.device), _stream())
+        if ctx.needs_input_grad[1]:
+            dw, acc = _grad_target(ctx.param, ctx.slot, wc)
+            _call("b200_conv2d_wgrad", _ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc)), *geom,
+                  *_ws_args(dy.device), _stream())
+        return dx, dw, None, None, None
+
+
+def conv2d(x, w, stride: int, padding: int, stats: Optional[torch.Tensor] = None):
+    return _Conv2d.apply(x, w, int(stride), int(padding), stats)
+
+
+# ---------------------------------------------------------------------------------------
+# batch norm (+ residual) (+ relu)
+# ---------------------------------------------------------------------------------------
+class BNWorkspace:
+    """Per-layer statistic accumulators.  ``fwd`` is filled by the producing conv's epilogue
+    (or by bn_stats), ``bwd`` by bn_bwd_reduce; each apply kernel zeroes the *other* buffer so
+    steady-state training needs no memset launches."""
+
+    def __init__(self, channels: int, device) -> None:
+        self.fwd = torch.zeros(2 * channels, dtype=torch.float32, device=device)
+        self.bwd = torch.zeros(2 * channels, dtype=torch.float32, device=device)
+        self.fwd_dirty = False
+        self.bwd_dirty = False
+
+    def begin_forward(self) -> None:
+        if self.fwd_dirty:           # previous forward was never followed by a backward
+            self.fwd.zero_()
+        self.fwd_dirty = True
+
+
+def bn_workspace(module, channels: int, device) -> BNWorkspace:
+    ws = module.__dict__.get("_b200_ws")
+    if ws is None or ws.fwd.device != device or ws.fwd.numel() != 2 * channels:
+        ws = BNWorkspace(channels, device)
+        module.__dict__["_b200_ws"] = ws
+    return ws
+
+
+class _BatchNormAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, rmean, rvar, nbt, residual, relu, training, momentum, eps, ws, stats_ready):
+        xc = _nhwc(x)
+        n, c, h, w = xc.shape
+        m = n * h * w
+        res = _nhwc(residual) if residual is not None else None
+        out = _empty_nhwc(n, c, h, w, x.device)
+        save_mean = torch.empty(c, dtype=torch.float32, device=x.device)
+        save_invstd = torch.empty(c, dtype=torch.float32, device=x.device)
+        if training and not stats_ready:
+            _call("b200_bn_stats", _ptr(xc), _ptr(ws.fwd), _i(m), _i(c), _stream())
+        _call("b200_bn_fwd_apply", _ptr(xc), _ptr(ws.fwd), _ptr(gamma), _ptr(beta), _ptr(res), _ptr(out),
+              _ptr(rmean), _ptr(rvar), _ptr(nbt), _ptr(save_mean), _ptr(save_invstd),
+              _ptr(ws.bwd), _i(ws.bwd.numel()), _i(m), _i(c), _f(momentum), _f(eps), _i(int(relu)),
+              _i(int(training)), _stream())
+        ws.bwd_dirty = False
+        ctx.save_for_backward(xc, out if relu else None, gamma, save_mean, save_invstd)
+        ctx.cfg = (m, c, bool(relu), residual is not None, training)
+        ctx.ws = ws
+        ctx.params = (gamma, beta)
+        ctx.slots = (getattr(gamma, "_grad_slot", None), getattr(beta, "_grad_slot", None))
+        if not training:
+            # eval: normalisation uses running stats; backward treats them as constants
+            pass
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xc, out, gamma, save_mean, save_invstd = ctx.saved_tensors
+        m, c, relu, has_res, training = ctx.cfg
+        ws = ctx.ws
+        dout = _nhwc(dout)
+        if not training:
+            raise RuntimeError("backward through eval-mode BatchNorm is not supported by the native kernels")
+        if ws.bwd_dirty:
+            ws.bwd.zero_()
+        _call("b200_bn_bwd_reduce", _ptr(dout), _ptr(out), _ptr(xc), _ptr(save_mean), _ptr(save_invstd),
+              _ptr(ws.bwd), _i(m), _i(c), _i(int(relu)), _stream())
+        ws.bwd_dirty = True
+        dx = torch.empty_like(xc, memory_format=torch.preserve_format)
+        dres = torch.empty_like(xc, memory_format=torch.preserve_format) if has_res else None
+        dgamma, _ = _grad_target(ctx.params[0], ctx.slots[0], gamma)
+        dbeta, _ = _grad_target(ctx.params[1], ctx.slots[1], gamma)
+        _call("b200_bn_bwd_apply", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean), _ptr(save_invstd),
+              _ptr(ws.bwd), _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0),
+              _ptr(ws.fwd), _i(ws.fwd.numel()), _i(m), _i(c), _i(int(relu)), _stream())
+        ws.fwd_dirty = False
+        return dx, dgamma, dbeta, None, None, None, dres, None, None, None, None, None, None
+
+
+def batch_norm_act(x, weight, bias, running_mean, running_var, num_batches_tracked, residual, relu,
+                   training, momentum, eps, ws: Optional[BNWorkspace] = None, stats_ready: bool = False):
+    if ws is None:
+        ws = BNWorkspace(x.shape[1], x.device)
+        stats_ready = False
+    elif not stats_ready and training:
+        ws.begin_forward()
+    return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, num_batches_tracked, residual,
+                               bool(relu), bool(training), float(momentum), float(eps), ws, bool(stats_ready))
+
+
+def conv_bn_act(x, conv_weight, stride, padding, bn, residual=None, relu=False):
+    """conv -> BN(+residual)(+ReLU) with the BN statistics accumulated by the conv epilogue."""
+    training = bn.training or not bn.track_running_stats
+    ws = bn_workspace(bn, conv_weight.shape[0], x.device)
+    if training:
+        ws.begin_forward()
+    y = conv2d(x, conv_weight, stride, padding, ws.fwd if training else None)
+    return batch_norm_act(
+        y, bn.weight, bn.bias, bn.running_mean if bn.track_running_stats else None,
+        bn.running_var if bn.track_running_stats else None,
+        bn.num_batches_tracked if (bn.training and bn.track_running_stats) else None,
+        residual, relu, training, 0.1 if bn.momentum is None else bn.momentum, bn.eps, ws, stats_ready=training)
+
+
+# ---------------------------------------------------------------------------------------
+# pooling
+# ---------------------------------------------------------------------------------------
+class _MaxPool3x3s2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xc = _nhwc(x)
+        n, c, h, w = xc.shape
+        p, q = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+        y = _empty_nhwc(n, c, p, q, x.device)
+        idx = torch.empty((n, p, q, c), dtype=torch.uint8, device=x.device)
+        _call("b200_maxpool3x3s2_fwd", _ptr(xc), _ptr(y), _ptr(idx), _i(n), _i(h), _i(w), _i(c), _stream())
+        ctx.save_for_backward(idx)
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        n, c, h, w = ctx.shape
+        dy = _nhwc(dy)
+        dx = _empty_nhwc(n, c, h, w, dy.device)
+        _call("b200_maxpool3x3s2_bwd", _ptr(dy), _ptr(idx), _ptr(dx), _i(n), _i(h), _i(w), _i(c), _stream())
+        return dx
+
+
+def max_pool_3x3s2(x):
+    return _MaxPool3x3s2.apply(x)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xc = _nhwc(x)
+        n, c, h, w = xc.shape
+        y = torch.empty((n, c), dtype=torch.float32, device=x.device)
+        _call("b200_avgpool_fwd", _ptr(xc), _ptr(y), _i(n), _i(h * w), _i(c), _stream())
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        n, c, h, w = ctx.shape
+        dy = dy.contiguous()
+        dx = _empty_nhwc(n, c, h, w, dy.device)
+        _call("b200_avgpool_bwd", _ptr(dy), _ptr(dx), _i(n), _i(h * w), _i(c), _stream())
+        return dx
+
+
+def global_avg_pool(x):
+    n, c, h, w = x.shape
+    if h * w == 1:
+        return _nhwc(x).reshape(n, c)      # identity for 1x1 maps (the dpp.py case): a view, no kernel
+    return _GlobalAvgPool.apply(x)
+
+
+# ---------------------------------------------------------------------------------------
+# linear = 1x1 convolution over a [M,1,1,K] tensor
+# ---------------------------------------------------------------------------------------
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x2 = x.reshape(-1, x.shape[-1]).contiguous().float()
+        wc = w.contiguous()
+        m, k = x2.shape
+        n = wc.shape[0]
+        y = torch.empty((m, n), dtype=torch.float32, device=x.device)
+        _call("b200_conv2d_fprop", _ptr(x2), _ptr(wc), _ptr(b), _ptr(y), _ptr(None),
+              _i(m), _i(1), _i(1), _i(k), _i(n), _i(1), _i(1), _i(1), _i(0), *_ws_args(x.device), _stream())
+        ctx.save_for_backward(x2, wc)
+        ctx.lead = x.shape[:-1]
+        ctx.params = (w, b)
+        ctx.slots = (getattr(w, "_grad_slot", None), getattr(b, "_grad_slot", None) if b is not None else None)
+        return y.reshape(*ctx.lead, n)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wc = ctx.saved_tensors
+        m, k = x2.shape
+        n = wc.shape[0]
+        dy2 = dy.reshape(m, n).contiguous()
+        geom = (_i(m), _i(1), _i(1), _i(k), _i(n), _i(1), _i(1), _i(1), _i(0))
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((m, k), dtype=torch.float32, device=dy.device)
+            _call("b200_conv2d_dgrad", _ptr(dy2), _ptr(wc), _ptr(dx), *geom, *_ws_args(dy.device), _stream())
+            dx = dx.reshape(*ctx.lead, k)
+        if ctx.needs_input_grad[1]:
+            dw, _ = _grad_target(ctx.params[0], ctx.slots[0], wc)
+            _call("b200_conv2d_wgrad", _ptr(dy2), _ptr(x2), _ptr(dw), _i(0), *geom, *_ws_args(dy.device), _stream())
+        if ctx.params[1] is not None and ctx.needs_input_grad[2]:
+            db, _ = _grad_target(ctx.params[1], ctx.slots[1], ctx.params[1])
+            _call("b200_colsum", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
+        return dx, dw, db
+
+
+def linear(x, w, b=None):
+    return _Linear.apply(x, w, b)
+
+
+# ---------------------------------------------------------------------------------------
+# loss
+# ---------------------------------------------------------------------------------------
+class _SoftmaxXent(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        z = logits.contiguous().float()
+        b, v = z.shape
+        loss = torch.empty((), dtype=torch.float32, device=z.device)
+        dz = torch.empty_like(z)
+        sc = scratch(z.device)
+        row = sc.row_loss if b <= sc.row_loss.numel() else torch.empty(b, dtype=torch.float32, device=z.device)
+        _call("b200_softmax_xent", _ptr(z), _ptr(target.contiguous()), _ptr(loss), _ptr(dz), _ptr(row), _i(b), _i(v),
+              _stream(), kernels=1 if b <= 32 else 2)
+        ctx.save_for_backward(dz)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (dz,) = ctx.saved_tensors
+        out = torch.empty_like(dz)
+        _call("b200_scale", _ptr(dz), _ptr(out), _sz(dz.numel()), _ptr(gout.contiguous()), _f(1.0), _stream())
+        return out, None
+
+
+def cross_entropy(logits, target):
+    return _SoftmaxXent.apply(logits, target)
+
+
+# ---------------------------------------------------------------------------------------
+# optimizers
+# ---------------------------------------------------------------------------------------
+def _dense_same_layout(ts: Sequence[torch.Tensor]) -> bool:
+    s0 = ts[0]
+    return all(t.is_non_overlapping_and_dense() and t.stride() == s0.stride() and t.dtype == torch.float32
+               for t in ts)
+
+
+class _OptimTable:
+    def __init__(self, ps, gs, s0s, s1s, device) -> None:
+        lib = load_library()
+        chunk = lib.b200_optim_chunk_elems()
+        assert lib.b200_optim_rec_bytes() == 48
+        recs = bytearray()
+        chunks = bytearray()
+        for ti, p in enumerate(ps):
+            tensors = [p, gs[ti]] + ([s0s[ti]] if s0s else []) + ([s1s[ti]] if s1s else [])
+            if not _dense_same_layout(tensors):
+                raise RuntimeError("fused optimizer needs dense fp32 tensors with identical strides")
+            recs += struct.pack("<QQQQqq", p.data_ptr(), gs[ti].data_ptr(), s0s[ti].data_ptr() if s0s else 0,
+                                s1s[ti].data_ptr() if s1s else 0, p.numel(), 0)
+            for c in range(-(-p.numel() // chunk)):
+                chunks += struct.pack("<ii", ti, c)
+        self.num_chunks = len(chunks) // 8
+        self.num_tensors = len(ps)
+        self.recs = torch.frombuffer(recs, dtype=torch.uint8).to(device)
+        self.chunks = torch.frombuffer(chunks, dtype=torch.uint8).to(device)
+        self.hyper = torch.zeros(16, dtype=torch.float32, device=device)
+        self.hyper_host: Optional[tuple] = None
+        self.step_ptrs = None
+
+    def set_hyper(self, vals: Sequence[float], keep_tail: int = 0) -> None:
+        vals = tuple(float(v) for v in vals)
+        if vals != self.hyper_host:
+            n = len(vals)
+            self.hyper[:n].copy_(torch.tensor(vals, dtype=torch.float32), non_blocking=False)
+            self.hyper_host = vals
+
+
+def _table(tables: dict, gi: int, ps, gs, s0s, s1s) -> _OptimTable:
+    key = (gi, tuple(p.data_ptr() for p in ps), tuple(g.data_ptr() for g in gs),
+           tuple(s.data_ptr() for s in (s0s or ())), tuple(s.data_ptr() for s in (s1s or ())))
+    tab = tables.get(gi)
+    if tab is None or tab[0] != key:
+        tab = (key, _OptimTable(ps, gs, s0s, s1s, ps[0].device))
+        tables[gi] = tab
+    return tab[1]
+
+
+def fused_sgd(tables: dict, gi: int, ps, gs, bufs, *, lr, momentum, dampening, weight_decay, nesterov, maximize,
+              first_step: bool, grad_scale: float = 1.0) -> None:
+    tab = _table(tables, gi, ps, gs, bufs, None)
+    tab.set_hyper((lr, momentum, dampening, weight_decay, float(nesterov), float(maximize), float(first_step), grad_scale))
+    _call("b200_fused_sgd", _ptr(tab.recs), _ptr(tab.chunks), _i(tab.num_chunks), _ptr(tab.hyper), _stream())
+
+
+def fused_adam(tables: dict, gi: int, ps, gs, ms, vs, steps, *, lr, beta1, beta2, eps, weight_decay, decoupled,
+               maximize, grad_scale: float = 1.0) -> None:
+    tab = _table(tables, gi, ps, gs, ms, vs)
+    if tab.step_ptrs is None:
+        ptrs = [s.data_ptr() if s.is_cuda else 0 for s in steps]
+        tab.step_ptrs = torch.tensor(ptrs, dtype=torch.int64).to(ps[0].device)
+        tab.hyper[8] = float(steps[0]) if steps else 0.0
+    tab.set_hyper((lr, beta1, beta2, eps, weight_decay, float(decoupled), float(maximize), grad_scale))
+    _call("b200_fused_adam", _ptr(tab.recs), _ptr(tab.chunks), _i(tab.num_chunks), _ptr(tab.hyper),
+          _ptr(tab.step_ptrs), _i(tab.num_tensors), _stream(), kernels=2)

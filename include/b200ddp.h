@@ -1,0 +1,88 @@
+/* C ABI of libb200ddp_kernels.so -- the sm_100a kernel library of distributeddataparallel_b200.
+ *
+ * Conventions
+ *   - every function launches asynchronously on `stream` and returns a cudaError_t as int
+ *     (0 = launched); nothing here allocates device memory: callers pass outputs and scratch;
+ *   - activations are NHWC ([N,H,W,C], C contiguous), filters KRSC ([K,R,S,C]), fp32 unless
+ *     a suffix says otherwise;
+ *   - "REF" cites /root/reference/dpp.py, "SURVEY Kn" the kernel inventory in SURVEY.md §2.5.
+ */
+#ifndef B200DDP_H_
+#define B200DDP_H_
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- input pipeline --------------------------------------------------------------------
+ * uint8 NHWC image batch -> fp32 NHWC, (x/255 - mean)/std: the ToTensor+Normalize transform
+ * of REF:32, done on the device after a 4x smaller H2D copy. */
+int b200_preprocess_u8(const uint8_t* in, float* out, size_t n, float mean, float stdv, cudaStream_t stream);
+
+/* ---- convolution as implicit GEMM (cuDNN on the reference path, REF:50-52).
+ * `workspace`/`counters` are split-K scratch: partial tiles and per-tile arrival tickets
+ * (counters must be zero on entry and are left zero).  `stats` (optional, [2*K], pre-zeroed
+ * or accumulating) receives per-output-channel sum and sum of squares for BatchNorm.
+ * A Linear layer is the R=S=H=W=1 case. */
+int b200_conv2d_fprop(const float* x, const float* w, const float* bias, float* y, float* stats,
+                      int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad,
+                      float* workspace, size_t workspace_bytes, unsigned* counters, int max_counters,
+                      cudaStream_t stream);
+int b200_conv2d_dgrad(const float* dy, const float* w, float* dx,
+                      int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad,
+                      float* workspace, size_t workspace_bytes, unsigned* counters, int max_counters,
+                      cudaStream_t stream);
+/* dw may point straight into a gradient-bucket slot (removes the reducer copy-in). */
+int b200_conv2d_wgrad(const float* dy, const float* x, float* dw, int accumulate,
+                      int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad,
+                      float* workspace, size_t workspace_bytes, unsigned* counters, int max_counters,
+                      cudaStream_t stream);
+
+/* ---- BatchNorm2d (+residual add, +ReLU) training kernels ------------------- */
+int b200_bn_stats(const float* x, float* sums, int M, int C, cudaStream_t stream);
+int b200_bn_fwd_apply(const float* x, const float* sums, const float* gamma, const float* beta,
+                      const float* residual, float* out, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, float* save_mean, float* save_invstd,
+                      float* zero_after, int zero_count, int M, int C, float momentum, float eps,
+                      int relu, int training, cudaStream_t stream);
+int b200_bn_bwd_reduce(const float* dy, const float* out, const float* x, const float* save_mean,
+                       const float* save_invstd, float* sums, int M, int C, int relu, cudaStream_t stream);
+int b200_bn_bwd_apply(const float* dy, const float* out, const float* x, const float* gamma,
+                      const float* save_mean, const float* save_invstd, const float* sums, float* dx,
+                      float* dres, float* dgamma, float* dbeta, int accumulate_param_grads,
+                      float* zero_after, int zero_count, int M, int C, int relu, cudaStream_t stream);
+
+/* ---- pooling --------------------------------------------------------------- */
+int b200_maxpool3x3s2_fwd(const float* x, float* y, uint8_t* idx, int Nb, int H, int W, int C, cudaStream_t stream);
+int b200_maxpool3x3s2_bwd(const float* dy, const uint8_t* idx, float* dx, int Nb, int H, int W, int C,
+                          cudaStream_t stream);
+int b200_avgpool_fwd(const float* x, float* y, int Nb, int HW, int C, cudaStream_t stream);
+int b200_avgpool_bwd(const float* dy, float* dx, int Nb, int HW, int C, cudaStream_t stream);
+
+/* ---- loss: mean softmax cross-entropy, forward and logits gradient in one launch
+ * (nn.CrossEntropyLoss at REF:40). `row_loss_scratch` needs B floats. */
+int b200_softmax_xent(const float* logits, const long long* target, float* loss, float* dlogits,
+                      float* row_loss_scratch, int B, int V, cudaStream_t stream);
+
+/* ---- small elementwise helpers ----------------------------------------------------------------- */
+int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, float scale_host, cudaStream_t stream);
+int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
+int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream);
+
+/* ---- fused multi-tensor optimizers (optim.SGD at REF:41,53) -------------------------
+ * recs: device array of {float* p, g, s0, s1; int64 n; int64 pad}; chunks: device array of
+ * {int tensor, int chunk}; hyper: device floats (layout in csrc/kernels/optim.cu). */
+int b200_optim_chunk_elems(void);
+int b200_optim_rec_bytes(void);
+int b200_fused_sgd(const void* recs, const void* chunks, int num_chunks, const float* hyper, cudaStream_t stream);
+int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float* hyper,
+                    float* const* step_ptrs, int num_tensors, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDP_H_ */
