@@ -34,6 +34,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("require_sync", &Reducer::require_sync)
       .def("set_comm", &Reducer::set_comm)
       .def("detach_hooks", &Reducer::detach_hooks)
+      .def("attach_hooks", &Reducer::attach_hooks)
       .def("num_buckets", &Reducer::num_buckets)
       .def("bucket_sizes", &Reducer::bucket_sizes)
       .def("bucket_params", &Reducer::bucket_params)

@@ -209,8 +209,15 @@ Reducer::Reducer(std::vector<at::Tensor> params, std::vector<std::vector<int64_t
   ready_.assign(params_.size(), 0);
   build_buckets(bucket_indices);
 
+  attach_hooks();
+}
+
+void Reducer::attach_hooks() {
   // One post hook per parameter on its gradient accumulator: fires after the gradient has
   // been accumulated into .grad for this backward pass (cf. reducer.hpp:74 autograd_hook).
+  // The accumulator node records the CUDA stream that is current when it is created; call
+  // this under the stream the training step runs on (see reattach_hooks()).
+  detach_hooks();
   accumulators_.reserve(params_.size());
   for (size_t i = 0; i < params_.size(); ++i) {
     TORCH_CHECK(params_[i].requires_grad(), "parameter ", names_[i], " does not require grad");

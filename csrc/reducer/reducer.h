@@ -90,6 +90,11 @@ class Reducer {
   bool require_sync() const { return require_sync_; }
   void set_comm(py::object comm) { comm_ = std::move(comm); }
   void detach_hooks();
+  // (Re)create the gradient-accumulator nodes under the CURRENT stream and hook them.  Needed
+  // before capturing a step into a CUDA graph on a side stream: autograd pins an accumulator
+  // to the stream it was created on, and a default-stream accumulator cannot be used while
+  // another stream is capturing.
+  void attach_hooks();
 
   // introspection
   int64_t num_buckets() const { return static_cast<int64_t>(buckets_.size()); }

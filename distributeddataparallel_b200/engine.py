@@ -65,11 +65,24 @@ class TrainStep:
 
         launches0 = native.launch_count()
         graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            out = self.model(static_x)
-            loss = self.criterion(out, static_y)
-            loss.backward()
-            self.optimizer.step()
+        cap_stream = torch.cuda.Stream()
+        cap_stream.wait_stream(torch.cuda.current_stream())
+        if self._ddp is not None:
+            # autograd pins a gradient accumulator to the stream it was created on: recreate them
+            # under the capture stream (and put them back on the caller's stream afterwards)
+            with torch.cuda.stream(cap_stream):
+                self._ddp.reducer.attach_hooks()
+        try:
+            with torch.cuda.graph(graph, stream=cap_stream):
+                out = self.model(static_x)
+                loss = self.criterion(out, static_y)
+                loss.backward()
+                self.optimizer.step()
+                # drop the autograd graph now: it keeps the capture-stream accumulator nodes alive
+                loss, out = loss.detach(), out.detach()
+        finally:
+            if self._ddp is not None:
+                self._ddp.reducer.attach_hooks()
         native.set_launches_per_capture(native.launch_count() - launches0)
         entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach(), "out": out.detach()}
         return entry

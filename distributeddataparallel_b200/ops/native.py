@@ -421,10 +421,19 @@ def cross_entropy(logits, target):
 # ---------------------------------------------------------------------------------------
 # optimizers
 # ---------------------------------------------------------------------------------------
+def _is_dense(t: torch.Tensor) -> bool:
+    """non-overlapping and dense: some permutation of the dims is contiguous."""
+    expect = 1
+    for size, stride in sorted(((sz, st) for sz, st in zip(t.shape, t.stride()) if sz != 1), key=lambda p: p[1]):
+        if stride != expect:
+            return False
+        expect *= size
+    return True
+
+
 def _dense_same_layout(ts: Sequence[torch.Tensor]) -> bool:
     s0 = ts[0]
-    return all(t.is_non_overlapping_and_dense() and t.stride() == s0.stride() and t.dtype == torch.float32
-               for t in ts)
+    return all(_is_dense(t) and t.stride() == s0.stride() and t.dtype == torch.float32 for t in ts)
 
 
 class _OptimTable:

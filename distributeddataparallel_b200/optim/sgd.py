@@ -47,10 +47,10 @@ class SGD(torch.optim.SGD):
                 for p in ps:
                     st = self.state[p]
                     if st.get("momentum_buffer") is None:
+                        # torch initialises the buffer with the first gradient (no dampening)
                         st["momentum_buffer"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                        st["_fresh"] = True
+                        first = True
                     bufs.append(st["momentum_buffer"])
-                first = any(self.state[p].pop("_fresh", False) for p in ps)
             native.fused_sgd(self._tables, gi, ps, [p.grad for p in ps], bufs, lr=group["lr"],
                              momentum=mom, dampening=group["dampening"], weight_decay=group["weight_decay"],
                              nesterov=group["nesterov"], maximize=group["maximize"], first_step=first)

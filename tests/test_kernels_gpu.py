@@ -164,9 +164,12 @@ def test_cross_entropy(nat, b, v):
 def test_preprocess_matches_torchvision_arithmetic(nat):
     u = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, device="cuda")
     out = nat.preprocess_u8(u)
-    ref = ((u.float() / 255.0) - 0.5) / 0.5
+    # torchvision runs ToTensor/Normalize on the host with true divisions; the CUDA scalar-div
+    # shortcut (multiply by reciprocal) is NOT the reference arithmetic
+    uc = u.cpu()
+    ref = (uc.float().div(255) - torch.tensor(0.5)).div(torch.tensor(0.5))
     assert out.shape == (32, 3, 32, 32) and out.is_contiguous(memory_format=torch.channels_last)
-    assert torch.equal(out.permute(0, 2, 3, 1), ref)
+    assert torch.equal(out.permute(0, 2, 3, 1).cpu(), ref)
 
 
 @pytest.mark.parametrize("momentum,wd,nesterov", [(0.0, 0.0, False), (0.9, 1e-4, False), (0.9, 0.0, True)])

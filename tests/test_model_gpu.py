@@ -22,10 +22,15 @@ def _exact_library_math():
 
 @pytest.mark.parametrize("batch", [32, 10])
 def test_simplecnn_native_matches_library_ops(batch):
+    """Native fp32 kernels vs the library ops, both judged against a float64 run of the same
+    model: BatchNorm over 32 (or 10) samples on 1x1 maps amplifies rounding differently per
+    implementation, so the fair yardstick is the distance to the fp64 answer."""
     torch.manual_seed(0)
     a = d.SimpleCNN().cuda()
     b = d.SimpleCNN().cuda()
+    c = d.SimpleCNN(channels_last=False).cuda().double()
     b.load_state_dict(a.state_dict())
+    c.load_state_dict(a.state_dict())
     x = d.ops.preprocess_u8(torch.randint(0, 256, (batch, 32, 32, 3), dtype=torch.uint8, device="cuda"))
     y = torch.randint(0, 10, (batch,), device="cuda")
     la = d.CrossEntropyLoss()(a(x), y)
@@ -33,12 +38,15 @@ def test_simplecnn_native_matches_library_ops(batch):
     d.ops.set_native(False)
     lb = d.CrossEntropyLoss()(b(x), y)
     lb.backward()
+    lc = d.CrossEntropyLoss()(c(x.double().contiguous()), y)
+    lc.backward()
     d.ops.set_native(True)
-    assert abs(float(la) - float(lb)) < 1e-4
-    worst = max(_rel(p.grad, q.grad) for p, q in zip(a.parameters(), b.parameters()))
-    assert worst < 5e-3, worst
-    for (n, p), (_, q) in zip(a.named_buffers(), b.named_buffers()):
-        assert torch.allclose(p.float(), q.float(), rtol=1e-3, atol=1e-5), n
+    assert abs(float(la) - float(lc)) < 1e-4 and abs(float(lb) - float(lc)) < 1e-4
+    err_native = max(_rel(p.grad, r.grad) for p, r in zip(a.parameters(), c.parameters()))
+    err_library = max(_rel(q.grad, r.grad) for q, r in zip(b.parameters(), c.parameters()))
+    assert err_native < max(3 * err_library, 2e-4), (err_native, err_library)
+    for (n, p), (_, r) in zip(a.named_buffers(), c.named_buffers()):
+        assert torch.allclose(p.double(), r.double(), rtol=1e-3, atol=1e-5), n
 
 
 def test_ddp_single_gpu_grads_land_in_bucket_slots():
@@ -60,27 +68,40 @@ def test_ddp_single_gpu_grads_land_in_bucket_slots():
 
 
 def test_graph_step_matches_eager():
-    def run(use_graph):
-        torch.manual_seed(0)
+    """A replayed step must equal the same step run eagerly from the same state.  (Whole
+    trajectories are not comparable: this model is chaotic -- BatchNorm over 32 samples on 1x1
+    maps -- and float atomics in the statistics differ in the last bit from run to run.)"""
+    def make():
         model = d.DDP(d.SimpleCNN().cuda(), device_ids=[0])
         opt = d.SGD(model.parameters(), lr=0.01)
-        step = d.TrainStep(model, d.CrossEntropyLoss(), opt, cuda_graph=use_graph)
-        g = torch.Generator(device="cpu").manual_seed(5)
-        losses = []
-        for i in range(8):
-            u = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
-            y = torch.randint(0, 10, (32,), generator=g).cuda()
-            losses.append(float(step(d.ops.preprocess_u8(u), y)))
-        return losses, step, [p.detach().clone() for p in model.parameters()], model
+        return model, opt
 
-    le, se, pe, _ = run(False)
-    lg, sg, pg, mg = run(True)
-    assert sg.captured and sg.replays >= 4 and se.replays == 0
-    for a, b in zip(le, lg):
-        assert abs(a - b) < 2e-3 * max(1.0, abs(a)), (le, lg)
-    assert max(_rel(a, b) for a, b in zip(pg, pe)) < 1e-3
-    nbt = mg.module.model.bn1.num_batches_tracked
-    assert int(nbt) == 8
+    def batch(g):
+        u = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).cuda()
+        return d.ops.preprocess_u8(u), torch.randint(0, 10, (32,), generator=g).cuda()
+
+    torch.manual_seed(0)
+    mg, og = make()
+    step_g = d.TrainStep(mg, d.CrossEntropyLoss(), og, cuda_graph=True)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    for _ in range(3):                         # eager settle: bucket rebuild happens here
+        step_g(*batch(g))
+    me, oe = make()
+    step_e = d.TrainStep(me, d.CrossEntropyLoss(), oe, cuda_graph=False)
+    for _ in range(3):                         # same number of eager steps so buckets are rebuilt too
+        step_e(*batch(torch.Generator(device="cpu").manual_seed(77)))
+    for k in range(3):
+        me.load_state_dict(mg.state_dict())    # same starting point for this step
+        x, y = batch(g)
+        le = float(step_e(x, y))
+        lg = float(step_g(x, y))
+        assert step_g.captured and step_g.replays >= k + 1 and step_e.replays == 0
+        assert abs(le - lg) < 1e-4 * max(1.0, abs(le)), (k, le, lg)
+        worst = max(_rel(a, b) for a, b in zip(mg.parameters(), me.parameters()))
+        assert worst < 1e-4, (k, worst)
+        for (n, a), (_, b) in zip(mg.named_buffers(), me.named_buffers()):
+            assert torch.allclose(a.float(), b.float(), rtol=1e-4, atol=1e-6), n
+    assert int(mg.module.model.bn1.num_batches_tracked) == 6
 
 
 def test_ragged_batch_falls_back_to_eager():
@@ -93,7 +114,7 @@ def test_ragged_batch_falls_back_to_eager():
         x = d.ops.preprocess_u8(torch.randint(0, 256, (b, 32, 32, 3), dtype=torch.uint8, device="cuda"))
         loss = step(x, torch.randint(0, 10, (b,), device="cuda"))
         assert torch.isfinite(loss)
-    assert step.replays >= 2 and step.eager_steps >= 4
+    assert step.replays >= 2 and step.eager_steps >= 3
 
 
 def test_device_loader_matches_cpu_pipeline():
