@@ -17,6 +17,8 @@
 // takes a ticket on a per-tile counter, and the last split to arrive sums the partials in a
 // fixed order (deterministic) and runs the epilogue.  The epilogue can also accumulate the
 // per-channel sum / sum-of-squares BatchNorm needs (fused statistics: saves one pass over Y).
+#include <stdio.h>
+
 #include "common.cuh"
 #include "b200ddp.h"
 
@@ -413,4 +415,90 @@ B200_API int b200_conv2d_wgrad(const float* dy, const float* x, float* dw, int a
   g.P = (H + 2 * pad - R) / stride + 1;
   g.Q = (W + 2 * pad - S) / stride + 1;
   return conv_dispatch(WGRAD, g, workspace_bytes, max_counters, stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward convolution for callers that must not allocate
+// ---------------------------------------------------------------------------------------------
+// Some hosts of this library cannot call cudaMalloc (or anything that calls it for them) at the
+// point where they need a convolution: code that runs while another stream of the process is
+// being captured into a CUDA graph (an allocation there invalidates the capture), plug-ins that
+// are handed a device and a stream by an embedding runtime that owns the memory budget, and
+// latency-critical loops that have already frozen their allocations.  b200_conv2d_fprop expects
+// such a caller to bring its own split-K scratch; this variant needs none, because its scratch
+// is a fixed array that is part of the library image.
+//
+// Layout of the built-in scratch: [tickets: 1024 x u32][partial tiles: 4 MiB].
+// Cost: every GPU that loads libb200ddp_kernels.so keeps these 4 MiB + 4 KiB until the process
+// exits, whether or not this entry point is ever called.
+namespace b200 {
+
+constexpr int kNoAllocMaxTiles = 1024;                         // 64x64 output tiles with a ticket each
+constexpr size_t kNoAllocTicketBytes = kNoAllocMaxTiles * sizeof(unsigned);
+constexpr size_t kNoAllocPartialBytes = (size_t)4 << 20;       // split-K partial tiles
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocTicketBytes + kNoAllocPartialBytes];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address; the
+// address each device maps it to is looked up once per device and cached here.
+static unsigned char* g_noalloc_base[kNoAllocMaxDevices] = {};
+static thread_local char g_noalloc_error[320] = "";
+
+static int noalloc_fail(cudaError_t code, const char* fmt, long long a = 0, long long b = 0) {
+  snprintf(g_noalloc_error, sizeof(g_noalloc_error), fmt, a, b);
+  return static_cast<int>(code);
+}
+
+}  // namespace b200
+
+B200_API const char* b200_conv2d_fprop_noalloc_error(void) { return g_noalloc_error; }
+
+B200_API size_t b200_conv2d_fprop_noalloc_scratch_bytes(void) { return kNoAllocTicketBytes + kNoAllocPartialBytes; }
+
+B200_API int b200_conv2d_fprop_noalloc(const float* x, const float* w, const float* bias, float* y, float* stats,
+                                       int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad,
+                                       cudaStream_t stream) {
+  g_noalloc_error[0] = '\0';
+  if (Nb <= 0 || H <= 0 || W <= 0 || C <= 0 || K <= 0 || R <= 0 || S <= 0 || stride <= 0 || pad < 0)
+    return noalloc_fail(cudaErrorInvalidValue, "b200_conv2d_fprop_noalloc: non-positive dimension");
+  const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+  if (P <= 0 || Q <= 0)
+    return noalloc_fail(cudaErrorInvalidValue, "b200_conv2d_fprop_noalloc: empty output (P=%lld, Q=%lld)", P, Q);
+  const long long tiles = ceil_div_ll((long long)Nb * P * Q, BM) * ceil_div_ll(K, BN);
+  if (tiles > kNoAllocMaxTiles)
+    return noalloc_fail(cudaErrorInvalidValue,
+                        "b200_conv2d_fprop_noalloc: output needs %lld tiles of 64x64 but the built-in scratch has "
+                        "tickets for %lld; use b200_conv2d_fprop with caller-provided scratch",
+                        tiles, (long long)kNoAllocMaxTiles);
+
+  // Once per device, with that device current: resolve the symbol to this device's address.
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return noalloc_fail(err, "b200_conv2d_fprop_noalloc: cudaGetDevice failed (%lld)", err);
+  if (dev < 0 || dev >= kNoAllocMaxDevices)
+    return noalloc_fail(cudaErrorInvalidDevice, "b200_conv2d_fprop_noalloc: device ordinal %lld not supported", dev);
+  unsigned char* base = g_noalloc_base[dev];
+  if (base == nullptr) {
+    void* p = nullptr;
+    err = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (err != cudaSuccess || p == nullptr)
+      return noalloc_fail(err != cudaSuccess ? err : cudaErrorInvalidSymbol,
+                          "b200_conv2d_fprop_noalloc: cudaGetSymbolAddress failed (%lld) on device %lld", err, dev);
+    base = g_noalloc_base[dev] = static_cast<unsigned char*>(p);
+  }
+  unsigned* tickets = reinterpret_cast<unsigned*>(base);
+  float* partials = reinterpret_cast<float*>(base + kNoAllocTicketBytes);
+
+  // The array keeps whatever the previous call left: tickets must start at zero (a launch that
+  // was interrupted could have left some behind); partial tiles are fully overwritten before use.
+  err = cudaMemsetAsync(tickets, 0, (size_t)tiles * sizeof(unsigned), stream);
+  if (err != cudaSuccess) return noalloc_fail(err, "b200_conv2d_fprop_noalloc: clearing tickets failed (%lld)", err);
+
+  ConvArgs g{};
+  g.a = x; g.b = w; g.out = y; g.bias = bias; g.stats = stats; g.workspace = partials; g.counters = tickets;
+  g.Nb = Nb; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.pad = pad; g.P = P; g.Q = Q;
+  const int rc = conv_dispatch(FPROP, g, kNoAllocPartialBytes, kNoAllocMaxTiles, stream);
+  if (rc != 0) noalloc_fail(static_cast<cudaError_t>(rc), "b200_conv2d_fprop_noalloc: kernel launch failed (%lld)", rc);
+  return rc;
 }

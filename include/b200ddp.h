@@ -42,6 +42,25 @@ int b200_conv2d_wgrad(const float* dy, const float* x, float* dw, int accumulate
                       float* workspace, size_t workspace_bytes, unsigned* counters, int max_counters,
                       cudaStream_t stream);
 
+/* Forward convolution that allocates nothing and needs no caller scratch.  No counterpart in the
+ * reference (REF has no native code); it exists for hosts that cannot call cudaMalloc where they
+ * need the op: code running while a sibling stream is being graph-captured, plug-ins inside a
+ * runtime that owns the device memory, loops that have frozen their allocations.  Same
+ * arithmetic and arguments as b200_conv2d_fprop minus the scratch parameters; split-K scratch is
+ * a 4 MiB + 4 KiB array inside the library image (held by every GPU that loads the library,
+ * until exit).
+ *   Limit: the output (N*P*Q x K) may span at most 1024 tiles of 64x64; larger problems return
+ *          cudaErrorInvalidValue and b200_conv2d_fprop_noalloc_error() explains why.
+ *   First call on a device resolves the array's device address (cudaGetSymbolAddress) -- make
+ *          that first call with the device current and before any stream capture begins.
+ *   All calls share the one array: calls that can overlap on the GPU (different streams, no
+ *          ordering between them) race on it.  Tickets are cleared at the start of every call. */
+int b200_conv2d_fprop_noalloc(const float* x, const float* w, const float* bias, float* y, float* stats,
+                              int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad,
+                              cudaStream_t stream);
+const char* b200_conv2d_fprop_noalloc_error(void);
+size_t b200_conv2d_fprop_noalloc_scratch_bytes(void);
+
 /* ---- BatchNorm2d (+residual add, +ReLU) training kernels ------------------- */
 int b200_bn_stats(const float* x, float* sums, int M, int C, cudaStream_t stream);
 int b200_bn_fwd_apply(const float* x, const float* sums, const float* gamma, const float* beta,
