@@ -1,0 +1,302 @@
+// Peer-to-peer collectives over NVLink-mapped memory: barrier, one-shot / two-shot all-reduce
+// (fused with the 1/world_size averaging and fp32<->bf16 handling), broadcast.  No NCCL.
+//
+// Reference path being replaced: /root/reference/dpp.py:21,39 -> torch DDP -> ProcessGroupNCCL
+// all-reduce of every gradient bucket, the constructor-time parameter
+// broadcast (K2) and the per-forward BatchNorm-buffer broadcast (K3).
+//
+// Memory model.  Every rank owns one "symmetric arena" (a cudaMalloc'd block mapped into all
+// peers through CUDA IPC); an object lives at the same offset in every rank's arena.  A rank
+// addresses peer p's copy as bufs[p] + offset: plain ld/st on those addresses travel over
+// NVLink 5 / NVSwitch.  Synchronisation is a flag exchange in the arenas' signal pads:
+//
+//     flag(dst, channel, block, src)  <- st.release.sys (epoch)       written by src into dst's pad
+//     wait                            <- ld.acquire.sys  >= epoch     dst spins on its own pad
+//
+// `epoch` is a per-(channel, block) counter kept in device memory and only ever incremented,
+// so flags are never reset (no reset race) and a CUDA graph can replay the kernels.  Spins are
+// bounded: a dead peer raises an error word instead of hanging the GPU.
+//
+// Algorithms (S = message bytes, N = ranks, in place on the arena object):
+//   one-shot : barrier | every rank loads all N copies, sums in rank order 0..N-1 (bit-identical
+//              everywhere), holds the result in registers | barrier | stores its own copy.
+//              Ingress (N-1)*S per GPU, 2 barriers: best for small messages.
+//   two-shot : barrier | rank r owns slice r: loads it from all N ranks, sums, scales, and PUSHES
+//              the result into slice r of all N arenas | barrier.  One pass; ingress and egress
+//              are both (N-1)/N*S and overlap (full duplex), so t >= (N-1)/N * S / B_link.
+//   broadcast: barrier | every rank pulls its 1/N slice from the root and pushes it to everyone |
+//              barrier (scatter + all-gather fused, root egress S instead of (N-1)*S).
+//
+// Test hook: with `emulate` set, blockIdx.y plays the rank and all "peers" are buffers on one
+// GPU, launched cooperatively so the spinning blocks are co-resident (the profiling guide
+// forbids mutually-waiting separate launches on one GPU).
+#include <cuda_bf16.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "b200ddp.h"
+
+namespace b200 {
+
+constexpr int kMaxRanks = 8;
+constexpr int kMaxCommBlocks = 128;          // flag rows per channel
+constexpr int kNumChannels = 4;              // independent flag/epoch sets (one per stream role)
+constexpr unsigned kSpinLimit = 400u * 1000u * 1000u;   // ~ tens of seconds of polling
+
+struct CommCtx {
+  unsigned char* bufs[kMaxRanks];   // arena base of every rank, as mapped in THIS process
+  uint32_t* flags[kMaxRanks];       // signal pad of every rank  [channel][block][src]
+  uint32_t* epochs;                 // local: [rank (emulation only)][channel][block]
+  uint32_t* error;                  // local error word
+  int rank, world, channel, emulate;
+};
+
+__device__ __forceinline__ int ctx_rank(const CommCtx& c) { return c.emulate ? (int)blockIdx.y : c.rank; }
+
+__device__ __forceinline__ uint32_t* flag_slot(const CommCtx& c, int dst, int block, int src) {
+  return c.flags[dst] + ((size_t)c.channel * kMaxCommBlocks + block) * kMaxRanks + src;
+}
+
+// All ranks' block `blockIdx.x` meet.  Acts as a system-scope release (before) / acquire (after).
+__device__ __forceinline__ void block_barrier(const CommCtx& c, int rank) {
+  __shared__ uint32_t epoch_s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* e = c.epochs + ((size_t)(c.emulate ? rank : 0) * kNumChannels + c.channel) * kMaxCommBlocks + blockIdx.x;
+    epoch_s = *e + 1u;
+    *e = epoch_s;
+  }
+  __syncthreads();
+  const uint32_t epoch = epoch_s;
+  if ((int)threadIdx.x < c.world) {
+    const int p = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(flag_slot(c, p, blockIdx.x, rank), epoch);
+    const uint32_t* mine = flag_slot(c, rank, blockIdx.x, p);
+    unsigned spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (++spins > kSpinLimit) {
+        atomicExch(c.error, 0xDEAD0000u | (uint32_t)p);   // peer p never arrived
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// ---- 16-byte vector helpers ----------------------------------------------------------------
+__device__ __forceinline__ uint4 ld_peer(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(void* p, uint4 v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename T> struct Vec;
+template <> struct Vec<float> {
+  __device__ static void acc(float (&a)[8], uint4 v) {
+    a[0] += __uint_as_float(v.x); a[1] += __uint_as_float(v.y);
+    a[2] += __uint_as_float(v.z); a[3] += __uint_as_float(v.w);
+  }
+  __device__ static uint4 pack(const float (&a)[8], float s) {
+    return make_uint4(__float_as_uint(a[0] * s), __float_as_uint(a[1] * s), __float_as_uint(a[2] * s),
+                      __float_as_uint(a[3] * s));
+  }
+};
+template <> struct Vec<__nv_bfloat16> {
+  __device__ static void acc(float (&a)[8], uint4 v) {     // bf16 pairs, accumulate in fp32
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      a[2 * i + 0] += __uint_as_float(w[i] << 16);
+      a[2 * i + 1] += __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+  __device__ static uint4 pack(const float (&a)[8], float s) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * i] * s, a[2 * i + 1] * s);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+// ---- two-shot (reduce-scatter + push all-gather in one pass) -----------------------------------
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c, size_t offset, size_t nvec,
+                                                                float scale) {
+  const int rank = ctx_rank(c), N = c.world;
+  block_barrier(c, rank);
+  const size_t per = (nvec + N - 1) / N;
+  const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
+  for (size_t i = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
+       i += (size_t)gridDim.x * blockDim.x) {
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N) v[p] = ld_peer(c.bufs[p] + offset + i * 16);
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N) Vec<T>::acc(a, v[p]);
+    const uint4 r = Vec<T>::pack(a, scale);
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N) st_peer(c.bufs[p] + offset + i * 16, r);
+  }
+  block_barrier(c, rank);
+}
+
+// ---- one-shot ------------------------------------------------------------------------------------
+constexpr int kOneShotVecPerThread = 4;
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c, size_t offset, size_t nvec,
+                                                                float scale) {
+  const int rank = ctx_rank(c), N = c.world;
+  block_barrier(c, rank);
+  uint4 res[kOneShotVecPerThread];
+  const size_t base = (size_t)blockIdx.x * blockDim.x * kOneShotVecPerThread + threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < kOneShotVecPerThread; ++k) {
+    const size_t i = base + (size_t)k * blockDim.x;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (i < nvec) {
+      uint4 v[kMaxRanks];
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < N) v[p] = ld_peer(c.bufs[p] + offset + i * 16);
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)          // fixed order 0..N-1: same bits on every rank
+        if (p < N) Vec<T>::acc(a, v[p]);
+    }
+    res[k] = Vec<T>::pack(a, scale);
+  }
+  block_barrier(c, rank);                          // everyone has read everything: safe to overwrite
+#pragma unroll
+  for (int k = 0; k < kOneShotVecPerThread; ++k) {
+    const size_t i = base + (size_t)k * blockDim.x;
+    if (i < nvec) *reinterpret_cast<uint4*>(c.bufs[rank] + offset + i * 16) = res[k];
+  }
+}
+
+// ---- broadcast (scatter from root + push all-gather) ------------------------------------------------
+__global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t offset, size_t nvec, int root) {
+  const int rank = ctx_rank(c), N = c.world;
+  block_barrier(c, rank);
+  const size_t per = (nvec + N - 1) / N;
+  const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
+  for (size_t i = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 v = ld_peer(c.bufs[root] + offset + i * 16);
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N && p != root) st_peer(c.bufs[p] + offset + i * 16, v);
+  }
+  block_barrier(c, rank);
+}
+
+__global__ void __launch_bounds__(32) barrier_kernel(const CommCtx c) { block_barrier(c, ctx_rank(c)); }
+
+template <typename K, typename... Args>
+static int launch_comm(K kernel, const CommCtx& c, int blocks, int threads, cudaStream_t st, Args... args) {
+  if (c.world < 1 || c.world > kMaxRanks || blocks < 1 || blocks > kMaxCommBlocks || c.channel < 0 ||
+      c.channel >= kNumChannels)
+    return static_cast<int>(cudaErrorInvalidValue);
+  if (c.emulate) {
+    CommCtx cc = c;
+    void* params[] = {(void*)&cc, (void*)&args...};
+    return static_cast<int>(cudaLaunchCooperativeKernel((const void*)kernel, dim3(blocks, c.world), dim3(threads),
+                                                        params, 0, st));
+  }
+  kernel<<<blocks, threads, 0, st>>>(c, args...);
+  return static_cast<int>(cudaPeekAtLastError());
+}
+
+static int pick_blocks(size_t nvec_per_rank, int max_blocks) {
+  size_t b = (nvec_per_rank + 512 * 4 - 1) / (512 * 4);
+  if (b < 1) b = 1;
+  if (b > (size_t)max_blocks) b = max_blocks;
+  return (int)b;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+B200_API int b200_comm_ctx_bytes(void) { return (int)sizeof(CommCtx); }
+B200_API int b200_comm_max_blocks(void) { return kMaxCommBlocks; }
+B200_API size_t b200_comm_signal_bytes(void) {
+  return (size_t)kNumChannels * kMaxCommBlocks * kMaxRanks * sizeof(uint32_t);
+}
+B200_API size_t b200_comm_epoch_bytes(void) {
+  return (size_t)kMaxRanks * kNumChannels * kMaxCommBlocks * sizeof(uint32_t);
+}
+B200_API size_t b200_allreduce_oneshot_max_bytes(void) {
+  return (size_t)kMaxCommBlocks * 512 * kOneShotVecPerThread * 16;
+}
+
+// dtype: 0 = fp32, 1 = bf16.  algo: 1 = one-shot, 2 = two-shot.  `nbytes` must be a multiple of 16.
+B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, int algo,
+                            int max_blocks, cudaStream_t stream) {
+  const CommCtx& c = *static_cast<const CommCtx*>(ctx);
+  if (nbytes % 16 != 0 || offset % 16 != 0) return static_cast<int>(cudaErrorInvalidValue);
+  const size_t nvec = nbytes / 16;
+  if (nvec == 0) return 0;
+  max_blocks = max(1, min(max_blocks, kMaxCommBlocks));
+  if (algo == 1) {
+    const size_t per_block = (size_t)512 * kOneShotVecPerThread;
+    const size_t blocks = (nvec + per_block - 1) / per_block;
+    if (blocks > (size_t)kMaxCommBlocks) return static_cast<int>(cudaErrorInvalidValue);   // too big for one-shot
+    if (dtype == 0)
+      return launch_comm(allreduce_oneshot_kernel<float>, c, (int)blocks, 512, stream, offset, nvec, scale);
+    return launch_comm(allreduce_oneshot_kernel<__nv_bfloat16>, c, (int)blocks, 512, stream, offset, nvec, scale);
+  }
+  const int blocks = pick_blocks((nvec + c.world - 1) / c.world, max_blocks);
+  if (dtype == 0) return launch_comm(allreduce_twoshot_kernel<float>, c, blocks, 512, stream, offset, nvec, scale);
+  return launch_comm(allreduce_twoshot_kernel<__nv_bfloat16>, c, blocks, 512, stream, offset, nvec, scale);
+}
+
+B200_API int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks,
+                            cudaStream_t stream) {
+  const CommCtx& c = *static_cast<const CommCtx*>(ctx);
+  if (nbytes % 16 != 0 || offset % 16 != 0 || root < 0 || root >= c.world)
+    return static_cast<int>(cudaErrorInvalidValue);
+  const size_t nvec = nbytes / 16;
+  if (nvec == 0) return 0;
+  const int blocks = pick_blocks((nvec + c.world - 1) / c.world, max(1, min(max_blocks, kMaxCommBlocks)));
+  return launch_comm(broadcast_kernel, c, blocks, 512, stream, offset, nvec, root);
+}
+
+B200_API int b200_barrier(const void* ctx, cudaStream_t stream) {
+  const CommCtx& c = *static_cast<const CommCtx*>(ctx);
+  return launch_comm(barrier_kernel, c, 1, 32, stream);
+}
+
+// ---- arena plumbing (cudaMalloc + CUDA IPC): control-plane helpers, called once at set-up ------------
+B200_API int b200_arena_alloc(size_t bytes, void** out) {
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  return static_cast<int>(cudaMemset(*out, 0, bytes));
+}
+B200_API int b200_arena_free(void* p) { return static_cast<int>(cudaFree(p)); }
+B200_API int b200_ipc_get_handle(void* p, unsigned char out[64]) {
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  static_assert(sizeof(h) == 64, "IPC handle size");
+  memcpy(out, &h, 64);
+  return 0;
+}
+B200_API int b200_ipc_open_handle(const unsigned char in[64], void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, in, 64);
+  return static_cast<int>(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+}
+B200_API int b200_ipc_close_handle(void* p) { return static_cast<int>(cudaIpcCloseMemHandle(p)); }

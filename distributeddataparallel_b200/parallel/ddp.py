@@ -137,12 +137,34 @@ class DistributedDataParallel(nn.Module):
             return comm
         if self.world_size == 1 and not dist.is_initialized():
             return NoComm()
-        if comm == "auto":
+        auto = comm == "auto"
+        if auto:
             comm = "p2p" if self.device.type == "cuda" and self.world_size > 1 else "c10d"
         if comm == "p2p":
             from .p2p import P2PComm
 
-            return P2PComm(self.process_group, self.device, algo=self.allreduce_algo)
+            grad_bytes = sum(p.numel() * p.element_size() for p in self._params)
+            buf_bytes = sum(b.numel() * b.element_size() + 16 for b in self.module.buffers())
+            p2p, ok = None, 1
+            try:
+                p2p = P2PComm(self.process_group, self.device, algo=self.allreduce_algo)
+                p2p.reserve(grad_bytes, buf_bytes)
+            except RuntimeError as e:
+                if not auto:
+                    raise
+                ok, self._p2p_error = 0, str(e)
+            if auto and self.world_size > 1:
+                # every rank must pick the same data plane
+                flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.process_group)
+                ok = int(flag.item())
+            if ok:
+                return p2p
+            import warnings
+
+            warnings.warn("P2P arena unavailable (%s); falling back to the c10d backend"
+                          % getattr(self, "_p2p_error", "a peer failed"))
+            return C10dComm(self.process_group)
         if comm in ("c10d", "nccl", "gloo"):
             return C10dComm(self.process_group)
         raise ValueError(f"unknown comm backend {comm!r}")

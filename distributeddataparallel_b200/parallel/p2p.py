@@ -1,0 +1,355 @@
+"""Symmetric arena + the P2P (NVLink) communication backend.
+
+This is the product data plane: gradient buckets, module buffers and broadcast staging live in
+a per-rank *symmetric arena* -- one ``cudaMalloc`` block whose CUDA-IPC handle every peer has
+opened, so that an object sits at the same offset in every rank's arena and each rank can
+``ld``/``st`` its peers' copies directly over NVLink 5 / NVSwitch.  The collectives are the
+kernels in ``csrc/kernels/comm.cu`` (barrier, one-shot and two-shot all-reduce fused with the
+1/world_size averaging, scatter+all-gather broadcast); there is no NCCL call on these paths.
+
+Replaces ProcessGroupNCCL on the reference's hot path (/root/reference/dpp.py:21,39; SURVEY.md
+§2.5(a) K2/K3/K4/K6, work items W2-W7).  The control plane -- exchanging the 64-byte IPC
+handles -- goes through ``torch.distributed`` (``all_gather_object``), as the north star allows.
+
+``EmulatedWorld`` runs the very same kernels with all "ranks" on one GPU in one cooperative
+launch; it exists so the collective logic can be tested on a single-GPU box.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import struct
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native
+from .comm import CommBase, _Done
+
+_DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1}
+HEADER_BYTES = 64 << 10          # signal pad + epoch counters + error word
+
+
+class _RawMem:
+    """Expose a raw device pointer to torch through __cuda_array_interface__ (no copy)."""
+
+    def __init__(self, ptr: int, nbytes: int) -> None:
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
+    return torch.as_tensor(_RawMem(ptr, nbytes), device=device)
+
+
+def _pack_ctx(bufs: Sequence[int], flags: Sequence[int], epochs: int, error: int, rank: int, world: int,
+              channel: int, emulate: int) -> ctypes.Array:
+    b = list(bufs) + [0] * (8 - len(bufs))
+    f = list(flags) + [0] * (8 - len(flags))
+    raw = struct.pack("<8Q8QQQ4i", *b, *f, epochs, error, rank, world, channel, emulate)
+    lib = native.load_library()
+    assert len(raw) == lib.b200_comm_ctx_bytes(), (len(raw), lib.b200_comm_ctx_bytes())
+    return ctypes.create_string_buffer(raw, len(raw))
+
+
+def _lib():
+    lib = native.load_library()
+    for name in ("b200_comm_signal_bytes", "b200_comm_epoch_bytes", "b200_allreduce_oneshot_max_bytes"):
+        getattr(lib, name).restype = ctypes.c_size_t
+    return lib
+
+
+class SymmetricArena:
+    """One IPC-shared device block per rank with a bump allocator (same sequence on all ranks)."""
+
+    def __init__(self, group, device: torch.device, nbytes: int) -> None:
+        lib = _lib()
+        self.group, self.device = group, device
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.nbytes = int(-(-nbytes // (2 << 20)) * (2 << 20))
+        assert lib.b200_comm_signal_bytes() + lib.b200_comm_epoch_bytes() + 256 <= HEADER_BYTES
+        torch.cuda.set_device(device)
+        ptr = ctypes.c_void_p()
+        rc = lib.b200_arena_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(ptr))
+        if rc != 0:
+            raise RuntimeError(f"arena cudaMalloc({self.nbytes}) failed: CUDA error {rc}")
+        self.base = int(ptr.value)
+        handle = (ctypes.c_ubyte * 64)()
+        rc = lib.b200_ipc_get_handle(ctypes.c_void_p(self.base), handle)
+        if rc != 0:
+            raise RuntimeError(f"cudaIpcGetMemHandle failed: CUDA error {rc}")
+        gathered: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(gathered, bytes(handle), group=group)
+        self.peer_base: List[int] = []
+        self._opened: List[int] = []
+        for r, h in enumerate(gathered):
+            if r == self.rank:
+                self.peer_base.append(self.base)
+                continue
+            out = ctypes.c_void_p()
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            rc = lib.b200_ipc_open_handle(buf, ctypes.byref(out))
+            if rc != 0:
+                raise RuntimeError(f"cudaIpcOpenMemHandle(rank {r}) failed: CUDA error {rc}; "
+                                   "peer access over NVLink is required for comm='p2p'")
+            self.peer_base.append(int(out.value))
+            self._opened.append(int(out.value))
+        self.memory = _as_tensor(self.base, self.nbytes, device)      # uint8 view of the local arena
+        self._cursor = HEADER_BYTES
+        sig = lib.b200_comm_signal_bytes()
+        self.epochs_ptr = self.base + sig
+        self.error_ptr = self.base + sig + lib.b200_comm_epoch_bytes()
+        self._ctx: Dict[int, ctypes.Array] = {}
+        dist.barrier(group=group)      # everyone has mapped everyone before the first kernel
+
+    def ctx(self, channel: int) -> ctypes.Array:
+        c = self._ctx.get(channel)
+        if c is None:
+            c = self._ctx[channel] = _pack_ctx(self.peer_base, self.peer_base, self.epochs_ptr, self.error_ptr,
+                                               self.rank, self.world, channel, 0)
+        return c
+
+    def alloc(self, nbytes: int, align: int = 256) -> int:
+        off = -(-self._cursor // align) * align
+        end = off + -(-int(nbytes) // 16) * 16
+        if end > self.nbytes:
+            raise RuntimeError(f"symmetric arena exhausted: need {end} of {self.nbytes} bytes "
+                               "(raise B200DDP_ARENA_MB)")
+        self._cursor = end
+        return off
+
+    def view(self, offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        return self.memory[offset:offset + nbytes].view(dtype)
+
+    def offset_of(self, t: torch.Tensor) -> Optional[int]:
+        off = t.data_ptr() - self.base
+        return off if 0 <= off and off + t.numel() * t.element_size() <= self.nbytes else None
+
+    def error_word(self) -> int:
+        off = self.error_ptr - self.base
+        return int(self.memory[off:off + 4].view(torch.int32).item()) & 0xFFFFFFFF
+
+    def close(self) -> None:
+        lib = native.load_library()
+        for p in self._opened:
+            lib.b200_ipc_close_handle(ctypes.c_void_p(p))
+        self._opened = []
+
+
+class _EventHandle:
+    def __init__(self, event: torch.cuda.Event) -> None:
+        self.event = event
+
+    def wait(self) -> None:
+        torch.cuda.current_stream().wait_event(self.event)
+
+
+class P2PComm(CommBase):
+    """Gradient buckets reduced by our NVLink kernels on a high-priority side stream."""
+
+    name = "p2p"
+    GRAD_CHANNEL, MAIN_CHANNEL = 0, 1
+
+    def __init__(self, process_group, device: torch.device, algo: str = "auto", arena_bytes: Optional[int] = None,
+                 max_blocks: Optional[int] = None) -> None:
+        super().__init__(process_group)
+        self.device = device
+        self.algo = algo
+        self.max_blocks = int(max_blocks or os.environ.get("B200DDP_COMM_BLOCKS", 32))
+        self.oneshot_max = int(os.environ.get("B200DDP_ONESHOT_MAX_BYTES", 256 << 10))
+        self._arena_bytes = arena_bytes
+        self.arena: Optional[SymmetricArena] = None
+        self.stream = torch.cuda.Stream(device=device, priority=-1)
+        self._staging: Optional[int] = None
+        self._staging_bytes = 0
+        self._buffer_region = None
+        self.bytes_reduced = 0
+
+    # -- arena ------------------------------------------------------------------------------
+    def reserve(self, grad_bytes: int, buffer_bytes: int = 0) -> None:
+        """Collective: size and create the arena (2 bucket generations + buffers + staging)."""
+        if self.arena is not None:
+            return
+        env = os.environ.get("B200DDP_ARENA_MB")
+        if self._arena_bytes is None:
+            staging = min(max(grad_bytes, 16 << 20), 256 << 20)
+            self._arena_bytes = (int(env) << 20) if env else int(2.3 * grad_bytes) + buffer_bytes + staging + (8 << 20)
+        self.arena = SymmetricArena(self.group, self.device, self._arena_bytes)
+
+    def _need_arena(self) -> SymmetricArena:
+        if self.arena is None:
+            self.reserve(256 << 20)
+        return self.arena
+
+    def allocate(self, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+        arena = self._need_arena()
+        esize = torch.empty((), dtype=dtype).element_size()
+        off = arena.alloc(int(numel) * esize)
+        t = arena.view(off, int(numel), dtype)
+        t.zero_()
+        return t
+
+    # -- collectives ------------------------------------------------------------------------
+    def _pick_algo(self, nbytes: int) -> int:
+        lib = _lib()
+        if self.algo == "oneshot" and nbytes <= lib.b200_allreduce_oneshot_max_bytes():
+            return 1
+        if self.algo in ("twoshot", "nvls"):
+            return 2
+        if self.algo == "auto" and nbytes <= self.oneshot_max:
+            return 1
+        return 2
+
+    def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype) -> None:
+        native._call("b200_allreduce", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
+                     ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.world_size),
+                     ctypes.c_int(self._pick_algo(nbytes)), ctypes.c_int(self.max_blocks),
+                     ctypes.c_void_p(stream.cuda_stream))
+
+    def launch(self, index: int, flat: torch.Tensor, is_last: bool):
+        self.launches += 1
+        if self.world_size == 1:
+            return _Done()
+        off = self.arena.offset_of(flat) if self.arena is not None else None
+        if off is None or flat.dtype not in _DTYPE_CODE:
+            raise RuntimeError("P2PComm can only reduce buckets that live in the symmetric arena (fp32 / bf16)")
+        nbytes = flat.numel() * flat.element_size()
+        cur = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self.stream.wait_event(ready)
+        self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype)
+        done = torch.cuda.Event()
+        done.record(self.stream)
+        self.bytes_reduced += nbytes
+        return _EventHandle(done)
+
+    def all_reduce_avg_(self, flat: torch.Tensor) -> None:
+        """In-place average on the current stream (tensor inside the arena, or staged through it)."""
+        cur = torch.cuda.current_stream(self.device)
+        off = self.arena.offset_of(flat) if self.arena is not None else None
+        if off is not None and flat.is_contiguous() and (flat.numel() * flat.element_size()) % 16 == 0:
+            self._allreduce_on(cur, self.MAIN_CHANNEL, off, flat.numel() * flat.element_size(), flat.dtype)
+            return
+        for view, stage_off, nbytes in self._staged_chunks(flat):
+            stage = self.arena.memory[stage_off:stage_off + view.numel() * view.element_size()].view(flat.dtype)
+            pad = nbytes - view.numel() * view.element_size()
+            stage.copy_(view)
+            if pad:
+                self.arena.memory[stage_off + nbytes - pad:stage_off + nbytes].zero_()
+            self._allreduce_on(cur, self.MAIN_CHANNEL, stage_off, nbytes, flat.dtype)
+            view.copy_(stage)
+
+    def _staged_chunks(self, flat: torch.Tensor):
+        arena = self._need_arena()
+        if self._staging is None:
+            self._staging_bytes = min(64 << 20, max(1 << 20, (arena.nbytes - arena._cursor) // 2))
+            self._staging = arena.alloc(self._staging_bytes)
+        flat1 = flat.reshape(-1)
+        esize = flat.element_size()
+        per = self._staging_bytes // esize
+        for s in range(0, flat1.numel(), per):
+            view = flat1[s:s + per]
+            nbytes = -(-view.numel() * esize // 16) * 16
+            yield view, self._staging, nbytes
+
+    def broadcast_(self, flat: torch.Tensor, src: int = 0) -> None:
+        if self.world_size == 1:
+            return
+        cur = torch.cuda.current_stream(self.device)
+        off = self.arena.offset_of(flat) if self.arena is not None else None
+        nb = flat.numel() * flat.element_size()
+        if off is not None and flat.is_contiguous() and nb % 16 == 0 and off % 16 == 0:
+            self._broadcast_on(cur, off, nb, src)
+            return
+        if not flat.is_contiguous():
+            raise ValueError("broadcast_ needs a contiguous tensor")
+        for view, stage_off, nbytes in self._staged_chunks(flat):
+            stage = self.arena.memory[stage_off:stage_off + view.numel() * view.element_size()].view(flat.dtype)
+            if self.rank == src:
+                stage.copy_(view)
+            self._broadcast_on(cur, stage_off, nbytes, src)
+            if self.rank != src:
+                view.copy_(stage)
+
+    def _broadcast_on(self, stream, off: int, nbytes: int, src: int) -> None:
+        native._call("b200_broadcast", self.arena.ctx(self.MAIN_CHANNEL), ctypes.c_size_t(off),
+                     ctypes.c_size_t(nbytes), ctypes.c_int(src), ctypes.c_int(self.max_blocks),
+                     ctypes.c_void_p(stream.cuda_stream))
+
+    def barrier(self) -> None:
+        if self.world_size > 1:
+            native._call("b200_barrier", self._need_arena().ctx(self.MAIN_CHANNEL),
+                         ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
+
+    # -- per-forward module-buffer sync (K3): one launch for every buffer of every dtype --------
+    def sync_buffers(self, module: torch.nn.Module, buffers: Sequence[torch.Tensor]) -> int:
+        if self.world_size == 1 or not buffers:
+            return 0
+        if self._buffer_region is None:
+            arena = self._need_arena()
+            total = sum(-(-b.numel() * b.element_size() // 16) * 16 for b in buffers)
+            base = arena.alloc(total)
+            off = base
+            with torch.no_grad():
+                for b in buffers:
+                    view = arena.view(off, b.numel(), b.dtype).view(b.shape)
+                    view.copy_(b)
+                    b.data = view                      # the module's buffer now lives in the arena
+                    off += -(-b.numel() * b.element_size() // 16) * 16
+            self._buffer_region = (base, total)
+        base, total = self._buffer_region
+        self._broadcast_on(torch.cuda.current_stream(self.device), base, total, 0)
+        return 1
+
+    def check(self) -> None:
+        """Raise if a kernel gave up waiting for a peer (bounded spin)."""
+        if self.arena is not None:
+            torch.cuda.synchronize(self.device)
+            w = self.arena.error_word()
+            if w:
+                raise RuntimeError(f"P2P collective timed out waiting for rank {w & 0xFFFF} (error word {w:#x})")
+
+
+class EmulatedWorld:
+    """All ranks on ONE GPU: same kernels, one cooperative launch with blockIdx.y as the rank."""
+
+    def __init__(self, world: int, device: torch.device | str = "cuda", arena_bytes: int = 64 << 20,
+                 max_blocks: int = 8) -> None:
+        lib = _lib()
+        self.world, self.device = world, torch.device(device)
+        self.nbytes = arena_bytes
+        self.max_blocks = max_blocks
+        self.arenas = [torch.zeros(arena_bytes, dtype=torch.uint8, device=self.device) for _ in range(world)]
+        self.epochs = torch.zeros(lib.b200_comm_epoch_bytes() // 4, dtype=torch.int32, device=self.device)
+        self.error = torch.zeros(64, dtype=torch.int32, device=self.device)
+        self.pads = [torch.zeros(lib.b200_comm_signal_bytes() // 4, dtype=torch.int32, device=self.device)
+                     for _ in range(world)]
+        bases = [a.data_ptr() for a in self.arenas]
+        pads = [p.data_ptr() for p in self.pads]
+        self._ctx = {ch: _pack_ctx(bases, pads, self.epochs.data_ptr(), self.error.data_ptr(), 0, world, ch, 1)
+                     for ch in range(2)}
+
+    def view(self, rank: int, offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        return self.arenas[rank][offset:offset + nbytes].view(dtype)
+
+    def allreduce(self, offset: int, nbytes: int, dtype: torch.dtype, algo: int, scale: Optional[float] = None,
+                  channel: int = 0) -> None:
+        native._call("b200_allreduce", self._ctx[channel], ctypes.c_size_t(offset), ctypes.c_size_t(nbytes),
+                     ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.world if scale is None else scale),
+                     ctypes.c_int(algo), ctypes.c_int(self.max_blocks),
+                     ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def broadcast(self, offset: int, nbytes: int, root: int, channel: int = 1) -> None:
+        native._call("b200_broadcast", self._ctx[channel], ctypes.c_size_t(offset), ctypes.c_size_t(nbytes),
+                     ctypes.c_int(root), ctypes.c_int(self.max_blocks),
+                     ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def barrier(self, channel: int = 1) -> None:
+        native._call("b200_barrier", self._ctx[channel], ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def error_word(self) -> int:
+        return int(self.error[0].item()) & 0xFFFFFFFF

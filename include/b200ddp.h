@@ -101,6 +101,28 @@ int b200_fused_sgd(const void* recs, const void* chunks, int num_chunks, const f
 int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float* hyper,
                     float* const* step_ptrs, int num_tensors, cudaStream_t stream);
 
+/* ---- peer-to-peer collectives over NVLink-mapped symmetric arenas (SURVEY K2-K6, W2-W7;
+ * ProcessGroupNCCL on the reference path, REF:21).  `ctx` points to a HOST copy of the CommCtx
+ * struct (csrc/kernels/comm.cu): arena and signal-pad base of every rank as mapped in this
+ * process, local epoch counters, error word, rank/world/channel.  Objects are addressed by
+ * byte offset inside the arena; all collectives are in place.
+ * dtype 0 = fp32, 1 = bf16 (fp32 accumulate); algo 1 = one-shot, 2 = two-shot. */
+int b200_comm_ctx_bytes(void);
+int b200_comm_max_blocks(void);
+size_t b200_comm_signal_bytes(void);
+size_t b200_comm_epoch_bytes(void);
+size_t b200_allreduce_oneshot_max_bytes(void);
+int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, int algo,
+                   int max_blocks, cudaStream_t stream);
+int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks, cudaStream_t stream);
+int b200_barrier(const void* ctx, cudaStream_t stream);
+/* set-up helpers (these DO allocate / map memory; call once, outside any capture) */
+int b200_arena_alloc(size_t bytes, void** out);
+int b200_arena_free(void* p);
+int b200_ipc_get_handle(void* p, unsigned char out[64]);
+int b200_ipc_open_handle(const unsigned char in[64], void** out);
+int b200_ipc_close_handle(void* p);
+
 #ifdef __cplusplus
 }
 #endif
