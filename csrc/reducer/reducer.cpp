@@ -287,7 +287,9 @@ void Reducer::build_buckets(const std::vector<std::vector<int64_t>>& bucket_indi
       const auto& p = params_[b.params[k]];
       at::Tensor v;
       if (p.is_non_overlapping_and_dense()) {
-        v = b.flat.as_strided(p.sizes(), p.strides(), b.offsets[k]);
+        // as_strided offsets are relative to the STORAGE, and `flat` may itself be a view into a
+        // larger allocation (the symmetric arena)
+        v = b.flat.as_strided(p.sizes(), p.strides(), b.flat.storage_offset() + b.offsets[k]);
       } else {
         v = b.flat.narrow(0, b.offsets[k], p.numel()).view(p.sizes());
       }

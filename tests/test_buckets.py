@@ -67,3 +67,37 @@ def test_param_metadata_compare():
     b = _C.pack_param_metadata([torch.empty(2, 3), torch.empty(5)])
     assert _C.compare_param_metadata(a, a.clone(), 1) == ""
     assert "size of dim 0" in _C.compare_param_metadata(a, b, 1)
+
+
+def test_reducer_slots_respect_allocator_storage_offset():
+    """Bucket memory may be a view into a bigger arena: slots must land inside that view."""
+    import torch.nn as nn
+
+    class Comm:
+        launches = 0
+
+        def launch(self, index, flat, is_last):
+            class H:
+                def wait(self):
+                    pass
+            return H()
+
+    arena = torch.zeros(10_000)
+    cursor = [1000]
+
+    def alloc(numel, dtype, device):
+        t = arena[cursor[0]:cursor[0] + numel]
+        cursor[0] += numel
+        return t
+
+    net = nn.Sequential(nn.Conv2d(3, 4, 3), nn.Linear(4, 2)).to(memory_format=torch.channels_last)
+    ps = list(net.parameters())
+    red = _C.Reducer(ps, [list(range(len(ps)))], Comm(), alloc, 1)
+    lo, hi = arena.data_ptr() + 1000 * 4, arena.data_ptr() + cursor[0] * 4
+    for i, p in enumerate(ps):
+        slot = red.grad_slot(i)
+        assert slot.shape == p.shape and slot.stride() == p.stride()
+        assert lo <= slot.data_ptr() and slot.data_ptr() + slot.numel() * 4 <= hi
+    red.grad_slot(0).fill_(1.0)
+    assert arena[:1000].abs().sum() == 0
+    red.detach_hooks()
