@@ -22,8 +22,10 @@
 //              everywhere), holds the result in registers | barrier | stores its own copy.
 //              Ingress (N-1)*S per GPU, 2 barriers: best for small messages.
 //   two-shot : barrier | rank r owns slice r: loads it from all N ranks, sums, scales, and PUSHES
-//              the result into slice r of all N arenas | barrier.  One pass; ingress and egress
-//              are both (N-1)/N*S and overlap (full duplex), so t >= (N-1)/N * S / B_link.
+//              the result into slice r of all N arenas | barrier.  One pass, no mid barrier (a
+//              thread overwrites only what it has already read).  Per GPU and direction the links
+//              carry (N-1)/N*S of loads plus (N-1)/N*S of pushes, so t >= 2(N-1)/N * S / B_link,
+//              i.e. bus bandwidth S/t*2(N-1)/N is bounded by the link bandwidth.
 //   broadcast: barrier | every rank pulls its 1/N slice from the root and pushes it to everyone |
 //              barrier (scatter + all-gather fused, root egress S instead of (N-1)*S).
 //
@@ -71,7 +73,8 @@ __device__ __forceinline__ void block_barrier(const CommCtx& c, int rank) {
   const uint32_t epoch = epoch_s;
   if ((int)threadIdx.x < c.world) {
     const int p = threadIdx.x;
-    __threadfence_system();
+    // st.release.sys is cumulative: it publishes this block's earlier peer stores (ordered
+    // before it by the bar.sync above) without a separate fence round trip
     st_release_sys(flag_slot(c, p, blockIdx.x, rank), epoch);
     const uint32_t* mine = flag_slot(c, rank, blockIdx.x, p);
     unsigned spins = 0;
@@ -129,27 +132,41 @@ template <> struct Vec<__nv_bfloat16> {
 };
 
 // ---- two-shot (reduce-scatter + push all-gather in one pass) -----------------------------------
-template <typename T>
+// NR = compile-time world size (0: runtime, up to kMaxRanks), U = vectors per thread per trip.
+// A thread issues all U*(N) 16-byte loads of a trip before consuming any, so U*(N-1) remote
+// requests per thread are in flight: NVLink latency (~2 us) is covered by memory-level
+// parallelism rather than by occupying more SMs.
+template <typename T, int NR, int U>
 __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c, size_t offset, size_t nvec,
                                                                 float scale) {
-  const int rank = ctx_rank(c), N = c.world;
+  constexpr int NMAX = NR ? NR : kMaxRanks;
+  const int rank = ctx_rank(c), N = NR ? NR : c.world;
   block_barrier(c, rank);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
-  for (size_t i = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
-       i += (size_t)gridDim.x * blockDim.x) {
-    uint4 v[kMaxRanks];
+  const size_t trip = (size_t)gridDim.x * blockDim.x * U;
+  for (size_t base = begin + (size_t)blockIdx.x * blockDim.x * U + threadIdx.x; base < end; base += trip) {
+    uint4 v[U][NMAX];
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
-      if (p < N) v[p] = ld_peer(c.bufs[p] + offset + i * 16);
-    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
-      if (p < N) Vec<T>::acc(a, v[p]);
-    const uint4 r = Vec<T>::pack(a, scale);
+      for (int p = 0; p < NMAX; ++p)
+        if (p < N && i < end) v[u][p] = ld_peer(c.bufs[p] + offset + i * 16);
+    }
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
-      if (p < N) st_peer(c.bufs[p] + offset + i * 16, r);
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i >= end) continue;
+      float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int p = 0; p < NMAX; ++p)
+        if (p < N) Vec<T>::acc(a, v[u][p]);
+      const uint4 r = Vec<T>::pack(a, scale);
+#pragma unroll
+      for (int p = 0; p < NMAX; ++p)
+        if (p < N) st_peer(c.bufs[p] + offset + i * 16, r);
+    }
   }
   block_barrier(c, rank);
 }
@@ -188,16 +205,27 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c,
 
 // ---- broadcast (scatter from root + push all-gather) ------------------------------------------------
 __global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t offset, size_t nvec, int root) {
+  constexpr int U = 8;
   const int rank = ctx_rank(c), N = c.world;
   block_barrier(c, rank);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
-  for (size_t i = begin + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < end;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const uint4 v = ld_peer(c.bufs[root] + offset + i * 16);
+  const size_t trip = (size_t)gridDim.x * blockDim.x * U;
+  for (size_t base = begin + (size_t)blockIdx.x * blockDim.x * U + threadIdx.x; base < end; base += trip) {
+    uint4 v[U];
 #pragma unroll
-    for (int p = 0; p < kMaxRanks; ++p)
-      if (p < N && p != root) st_peer(c.bufs[p] + offset + i * 16, v);
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i < end) v[u] = ld_peer(c.bufs[root] + offset + i * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i >= end) continue;
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < N && p != root) st_peer(c.bufs[p] + offset + i * 16, v[u]);
+    }
   }
   block_barrier(c, rank);
 }
@@ -220,7 +248,7 @@ static int launch_comm(K kernel, const CommCtx& c, int blocks, int threads, cuda
 }
 
 static int pick_blocks(size_t nvec_per_rank, int max_blocks) {
-  size_t b = (nvec_per_rank + 512 * 4 - 1) / (512 * 4);
+  size_t b = (nvec_per_rank + 512 * 8 - 1) / (512 * 8);
   if (b < 1) b = 1;
   if (b > (size_t)max_blocks) b = max_blocks;
   return (int)b;
@@ -259,8 +287,16 @@ B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int d
     return launch_comm(allreduce_oneshot_kernel<__nv_bfloat16>, c, (int)blocks, 512, stream, offset, nvec, scale);
   }
   const int blocks = pick_blocks((nvec + c.world - 1) / c.world, max_blocks);
-  if (dtype == 0) return launch_comm(allreduce_twoshot_kernel<float>, c, blocks, 512, stream, offset, nvec, scale);
-  return launch_comm(allreduce_twoshot_kernel<__nv_bfloat16>, c, blocks, 512, stream, offset, nvec, scale);
+#define B200_TWOSHOT(T)                                                                                          \
+  switch (c.world) {                                                                                             \
+    case 2: return launch_comm(allreduce_twoshot_kernel<T, 2, 8>, c, blocks, 512, stream, offset, nvec, scale);  \
+    case 4: return launch_comm(allreduce_twoshot_kernel<T, 4, 4>, c, blocks, 512, stream, offset, nvec, scale);  \
+    case 8: return launch_comm(allreduce_twoshot_kernel<T, 8, 2>, c, blocks, 512, stream, offset, nvec, scale);  \
+    default: return launch_comm(allreduce_twoshot_kernel<T, 0, 1>, c, blocks, 512, stream, offset, nvec, scale); \
+  }
+  if (dtype == 0) { B200_TWOSHOT(float) }
+  B200_TWOSHOT(__nv_bfloat16)
+#undef B200_TWOSHOT
 }
 
 B200_API int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks,

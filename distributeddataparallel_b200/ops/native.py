@@ -87,6 +87,7 @@ class _Scratch:
         self.workspace = torch.empty(self.WORKSPACE_BYTES // 4, dtype=torch.float32, device=device)
         self.counters = torch.zeros(self.MAX_COUNTERS, dtype=torch.int32, device=device)
         self.row_loss = torch.empty(1 << 16, dtype=torch.float32, device=device)
+        self.error = torch.zeros(16, dtype=torch.int32, device=device)     # tcgen05 wait-timeout word
 
 
 _scratch: Dict[int, _Scratch] = {}
@@ -103,6 +104,71 @@ def scratch(device: torch.device) -> _Scratch:
 def _ws_args(dev: torch.device):
     s = scratch(dev)
     return (_ptr(s.workspace), _sz(s.WORKSPACE_BYTES), _ptr(s.counters), _i(s.MAX_COUNTERS))
+
+
+# ---------------------------------------------------------------------------------------
+# tensor-core (tcgen05) path switch
+# ---------------------------------------------------------------------------------------
+import os as _os
+
+_tensor_cores = _os.environ.get("B200DDP_TC", "1") != "0"
+_NOT_SUPPORTED = 801          # cudaErrorNotSupported: shape needs the FFMA fallback
+tc_launches = 0
+ffma_launches = 0
+
+
+def set_tensor_cores(enabled: bool) -> None:
+    """Route convolutions / linears through the tcgen05 kernels (TF32 math) when True."""
+    global _tensor_cores
+    _tensor_cores = bool(enabled)
+
+
+def tensor_cores_enabled() -> bool:
+    return _tensor_cores
+
+
+def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device) -> None:
+    """Try `<name>_tc` (tcgen05) first, fall back to the FFMA kernel for unsupported shapes."""
+    global _launches, tc_launches, ffma_launches
+    if _tensor_cores:
+        lib = load_library()
+        s = scratch(dev)
+        rc = getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+        if rc == 0:
+            _launches += 1
+            tc_launches += 1
+            return
+        if rc != _NOT_SUPPORTED:
+            raise RuntimeError(f"{name}_tc failed: CUDA error {rc}")
+    ffma_launches += 1
+    if name == "b200_conv2d_fprop":
+        x, w, y, stats = head
+        _call(name, x, w, _ptr(None), y, stats, *geom, *_ws_args(dev), _stream())
+    else:
+        _call(name, *head, *geom, *_ws_args(dev), _stream())
+
+
+def tc_error_word(device=None) -> int:
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    return int(scratch(dev).error[0].item()) & 0xFFFFFFFF
+
+
+def gemm_tc(a: torch.Tensor, b: torch.Tensor, mode: int, bias: Optional[torch.Tensor] = None,
+            out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """Dense tcgen05 GEMM, fp32 output.  mode 0: a[M,K] b[N,K]^T; 1: a[M,K] b[K,N]; 2: a[K,M]^T b[K,N]."""
+    assert a.dtype == b.dtype and a.dtype in (torch.float32, torch.bfloat16) and a.is_contiguous() and b.is_contiguous()
+    if mode == 0:
+        (m, k), n = a.shape, b.shape[0]
+    elif mode == 1:
+        (m, k), n = a.shape, b.shape[1]
+    else:
+        (k, m), n = a.shape, b.shape[1]
+    if out is None:
+        out = torch.empty((m, n), dtype=torch.float32, device=a.device)
+    s = scratch(a.device)
+    _call("b200_gemm_tc", _ptr(a), _ptr(b), _ptr(out), _ptr(bias), _i(m), _i(n), _i(k), _i(mode),
+          _i(int(a.dtype == torch.bfloat16)), _i(int(accumulate)), *_ws_args(a.device), _ptr(s.error), _stream())
+    return out
 
 
 # ---------------------------------------------------------------------------------------
@@ -156,8 +222,8 @@ class _Conv2d(torch.autograd.Function):
         xc, wc = _nhwc(x), _nhwc(w)
         n, h, wd, c, k, r, s, p, q = _conv_geom(xc, wc, stride, pad)
         y = _empty_nhwc(n, k, p, q, x.device)
-        _call("b200_conv2d_fprop", _ptr(xc), _ptr(wc), _ptr(None), _ptr(y), _ptr(stats),
-              _i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad), *_ws_args(x.device), _stream())
+        _conv_call("b200_conv2d_fprop", (_ptr(xc), _ptr(wc), _ptr(y), _ptr(stats)),
+                   (_i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad)), x.device)
         ctx.save_for_backward(xc, wc)
         ctx.geom = (n, h, wd, c, k, r, s, stride, pad)
         ctx.param = w
@@ -173,11 +239,10 @@ class _Conv2d(torch.autograd.Function):
         dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = _empty_nhwc(n, c, h, wd, dy.device)
-            _call("b200_conv2d_dgrad", _ptr(dy), _ptr(wc), _ptr(dx), *geom, *_ws_args(dy.device), _stream())
+            _conv_call("b200_conv2d_dgrad", (_ptr(dy), _ptr(wc), _ptr(dx)), geom, dy.device)
         if ctx.needs_input_grad[1]:
             dw, acc = _grad_target(ctx.param, ctx.slot, wc)
-            _call("b200_conv2d_wgrad", _ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc)), *geom,
-                  *_ws_args(dy.device), _stream())
+            _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device)
         return dx, dw, None, None, None
 
 

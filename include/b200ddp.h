@@ -101,6 +101,26 @@ int b200_fused_sgd(const void* recs, const void* chunks, int num_chunks, const f
 int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float* hyper,
                     float* const* step_ptrs, int num_tensors, cudaStream_t stream);
 
+/* ---- tcgen05 / TMEM tensor-core path (csrc/kernels/gemm_tcgen05.cu) ------------
+ * Dense GEMM with fp32 output; inputs fp32 (TF32 math) or bf16.  mode 0: A[M,K] B[N,K]^T,
+ * mode 1: A[M,K] B[K,N], mode 2: A[K,M]^T B[K,N].  Dimensions that are contiguous in memory
+ * must be multiples of 4 (fp32) / 8 (bf16).  `error` (optional device word) is set if an
+ * internal wait times out.  The conv entry points return cudaErrorNotSupported (801) for
+ * shapes that need the FFMA fallback (channels not a multiple of 4). */
+int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, int M, int N, int K, int mode,
+                 int bf16, int accumulate, float* workspace, size_t workspace_bytes, unsigned* counters,
+                 int max_counters, unsigned* error, cudaStream_t stream);
+int b200_conv2d_fprop_tc(const float* x, const float* w, float* y, float* stats, int Nb, int H, int W, int C,
+                         int K, int R, int S, int stride, int pad, float* workspace, size_t workspace_bytes,
+                         unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
+int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, int Nb, int H, int W, int C, int K,
+                         int R, int S, int stride, int pad, float* workspace, size_t workspace_bytes,
+                         unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
+int b200_conv2d_wgrad_tc(const float* dy, const float* x, float* dw, int accumulate, int Nb, int H, int W,
+                         int C, int K, int R, int S, int stride, int pad, float* workspace,
+                         size_t workspace_bytes, unsigned* counters, int max_counters, unsigned* error,
+                         cudaStream_t stream);
+
 /* ---- peer-to-peer collectives over NVLink-mapped symmetric arenas (SURVEY K2-K6, W2-W7;
  * ProcessGroupNCCL on the reference path, REF:21).  `ctx` points to a HOST copy of the CommCtx
  * struct (csrc/kernels/comm.cu): arena and signal-pad base of every rank as mapped in this

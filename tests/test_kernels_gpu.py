@@ -15,7 +15,9 @@ def nat():
     native.load_library()
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    return native
+    native.set_tensor_cores(False)       # this module checks the exact-fp32 FFMA kernels
+    yield native
+    native.set_tensor_cores(True)
 
 
 def _cl(t):

@@ -1,0 +1,93 @@
+"""tcgen05 / TMEM kernels vs float64 references: dense GEMM (3 operand layouts, TF32 and bf16)
+and implicit-GEMM convolution fprop / dgrad / wgrad on the dpp.py layer shapes."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from distributeddataparallel_b200.ops import native
+
+    native.load_library()
+    return native
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-12))
+
+
+def _cl(t):
+    return t.contiguous(memory_format=torch.channels_last)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-3), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (256, 128, 512), (32, 16, 512), (1000, 200, 328), (4096, 1024, 1024)])
+def test_dense_gemm_three_layouts(nat, dtype, tol, m, n, k):
+    torch.manual_seed(0)
+    a = torch.randn(m, k, device="cuda").to(dtype)
+    b_nk = torch.randn(n, k, device="cuda").to(dtype)
+    ref = a.double() @ b_nk.double().t()
+    out = nat.gemm_tc(a, b_nk, 0)
+    assert _rel(out, ref) < tol, ("NT", _rel(out, ref))
+    b_kn = b_nk.t().contiguous()
+    out = nat.gemm_tc(a, b_kn, 1)
+    assert _rel(out, ref) < tol, ("NN", _rel(out, ref))
+    a_km = a.t().contiguous()
+    out = nat.gemm_tc(a_km, b_kn, 2)
+    assert _rel(out, ref) < tol, ("TN", _rel(out, ref))
+    assert nat.tc_error_word() == 0
+
+
+def test_dense_gemm_bias_and_accumulate(nat):
+    a = torch.randn(64, 256, device="cuda")
+    b = torch.randn(48, 256, device="cuda")
+    bias = torch.randn(48, device="cuda")
+    out = nat.gemm_tc(a, b, 0, bias=bias)
+    ref = a.double() @ b.double().t() + bias.double()
+    assert _rel(out, ref) < 2e-3
+    out2 = nat.gemm_tc(a, b, 0, out=out.clone(), accumulate=True)
+    assert _rel(out2, 2 * ref - bias.double()) < 2e-3
+
+
+CONV_SHAPES = [
+    (32, 64, 8, 64, 3, 1, 1), (32, 64, 8, 128, 3, 2, 1), (32, 128, 4, 128, 3, 1, 1), (32, 64, 8, 128, 1, 2, 0),
+    (32, 128, 4, 256, 3, 2, 1), (32, 256, 2, 256, 3, 1, 1), (32, 256, 2, 512, 3, 2, 1), (32, 512, 1, 512, 3, 1, 1),
+    (32, 256, 2, 512, 1, 2, 0), (10, 64, 8, 64, 3, 1, 1), (10, 512, 1, 512, 3, 1, 1), (8, 64, 56, 64, 3, 1, 1),
+    (8, 256, 14, 1024, 1, 1, 0),
+]
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_conv_tc_matches_fp64(nat, shape):
+    n, cin, h, cout, r, stride, pad = shape
+    torch.manual_seed(1)
+    nat.set_tensor_cores(True)
+    before = nat.tc_launches
+    x = _cl(torch.randn(n, cin, h, h, device="cuda")).requires_grad_(True)
+    w = _cl(torch.randn(cout, cin, r, r, device="cuda") * 0.1).requires_grad_(True)
+    stats = torch.zeros(2 * cout, device="cuda")
+    y = nat.conv2d(x, w, stride, pad, stats)
+    xd, wd = x.detach().double().requires_grad_(True), w.detach().double().requires_grad_(True)
+    ref = F.conv2d(xd, wd, None, stride, pad)
+    assert _rel(y, ref) < 2e-3, _rel(y, ref)
+    assert torch.allclose(stats[:cout].double(), ref.sum(dim=(0, 2, 3)), rtol=2e-2, atol=0.5)
+    assert torch.allclose(stats[cout:].double(), (ref * ref).sum(dim=(0, 2, 3)), rtol=2e-2, atol=0.5)
+    dy = _cl(torch.randn_like(y))
+    gx, gw = torch.autograd.grad(y, (x, w), dy)
+    rx, rw = torch.autograd.grad(ref, (xd, wd), dy.double())
+    assert _rel(gx, rx) < 2e-3 and _rel(gw, rw) < 2e-3, (_rel(gx, rx), _rel(gw, rw))
+    assert nat.tc_launches - before == 3, "all three passes must have run on the tcgen05 kernel"
+    assert nat.tc_error_word() == 0
+
+
+def test_stem_falls_back_to_ffma(nat):
+    nat.set_tensor_cores(True)
+    before = nat.ffma_launches
+    x = _cl(torch.randn(4, 3, 32, 32, device="cuda"))
+    w = _cl(torch.randn(64, 3, 7, 7, device="cuda"))
+    y = nat.conv2d(x, w, 2, 3)
+    assert nat.ffma_launches == before + 1
+    assert _rel(y, F.conv2d(x.double(), w.double(), None, 2, 3)) < 1e-5
