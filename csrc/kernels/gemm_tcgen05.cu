@@ -11,8 +11,8 @@
 //
 //   warps 0-7  producers : gather 16-byte chunks of A and B with cp.async (zero-fill for
 //                          padding / out-of-range) straight into the UMMA canonical shared-memory
-//                          layouts (K-major and 16-bit MN-major: no-swizzle core matrices; 32-bit
-//                          MN-major: SWIZZLE_128B_BASE32B), 4-stage ring, then
+//                          layouts (K-major: SWIZZLE_128B; 16-bit MN-major: no-swizzle core
+//                          matrices; 32-bit MN-major: SWIZZLE_128B_BASE32B), 4-stage ring, then
 //                          fence.proxy.async + mbarrier arrive on full[stage]
 //   warp  8    MMA issuer: one elected thread waits full[stage], issues 4 x tcgen05.mma
 //                          (kind::tf32 K=8 or kind::f16 K=16, M=128, N=BN, accumulator in TMEM),
@@ -53,8 +53,33 @@ constexpr unsigned kWaitLimit = 1u << 28;
 enum Kind { DENSE_K = 0, IM2COL_K = 1, IM2COL_T_K = 2, DENSE_MN = 3, WEIGHT_T_MN = 4, IM2COL_MN = 5 };
 __host__ __device__ constexpr bool is_mn(int kind) { return kind >= DENSE_MN; }
 
+// Division by a launch-time constant as multiply-high + shift (valid for numerators < 2^31):
+// the operand gathers decode (pixel, filter tap, channel) for every 16-byte chunk.
+struct FastDiv {
+  int d;
+  unsigned mul, shr;
+  __device__ __forceinline__ int div(int n) const { return d == 1 ? n : (int)(__umulhi((unsigned)n, mul) >> shr); }
+  __device__ __forceinline__ void divmod(int n, int& q, int& r) const {
+    q = div(n);
+    r = n - q * d;
+  }
+};
+static FastDiv make_fastdiv(int d) {
+  FastDiv f{};
+  f.d = d < 1 ? 1 : d;
+  if (f.d > 1) {
+    int lg = 0;
+    while ((1ll << lg) < f.d) ++lg;                       // ceil(log2 d)
+    const unsigned p = 31 + lg;
+    f.mul = (unsigned)(((1ull << p) + (unsigned)f.d - 1) / (unsigned)f.d);
+    f.shr = p - 32;
+  }
+  return f;
+}
+
 struct Geom {
   int Nb, H, W, C, K, R, S, P, Q, stride, pad;
+  FastDiv fQ, fP, fC, fS, fW, fH, fK, fStride;
 };
 
 struct Args {
@@ -161,84 +186,133 @@ __host__ __device__ constexpr uint32_t make_idesc(bool bf16, bool a_mn, bool b_m
          ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
-// ---- operand chunk addressing ------------------------------------------------------------------
-// Returns the global address of the 16-byte chunk starting at element (mn, k) and whether it is
-// in range (false -> the chunk is zero-filled).  ES = element size in bytes.
-template <int KIND, int ES>
-__device__ __forceinline__ const char* chunk_src(const void* base, long long ld, const Geom& g, int mn, int k,
-                                                 int mn_limit, int k_limit, bool& valid) {
-  const char* p = static_cast<const char*>(base);
-  valid = (mn < mn_limit) && (k < k_limit);
-  if (!valid) return p;
-  if (KIND == DENSE_K) return p + ((long long)mn * ld + k) * ES;
-  if (KIND == DENSE_MN) return p + ((long long)k * ld + mn) * ES;
-  if (KIND == IM2COL_K) {
-    const int q = mn % g.Q, pp = (mn / g.Q) % g.P, n = mn / (g.Q * g.P);
-    const int c = k % g.C, rs = k / g.C, s = rs % g.S, r = rs / g.S;
-    const int h = pp * g.stride - g.pad + r, w = q * g.stride - g.pad + s;
-    valid = h >= 0 && h < g.H && w >= 0 && w < g.W;
-    return valid ? p + (((long long)(n * g.H + h) * g.W + w) * g.C + c) * ES : p;
-  }
-  if (KIND == IM2COL_T_K) {
-    const int w = mn % g.W, h = (mn / g.W) % g.H, n = mn / (g.W * g.H);
-    const int co = k % g.K, rs = k / g.K, s = rs % g.S, r = rs / g.S;
-    const int hh = h + g.pad - r, ww = w + g.pad - s;
-    const int pp = hh / g.stride, q = ww / g.stride;
-    valid = hh >= 0 && ww >= 0 && (hh % g.stride) == 0 && (ww % g.stride) == 0 && pp < g.P && q < g.Q;
-    return valid ? p + (((long long)(n * g.P + pp) * g.Q + q) * g.K + co) * ES : p;
-  }
-  if (KIND == WEIGHT_T_MN) {
-    const int co = k % g.K, rs = k / g.K;
-    return p + (((long long)co * g.R * g.S + rs) * g.C + mn) * ES;
-  }
-  // IM2COL_MN: k = output pixel, mn = (r, s, c)
-  {
-    const int q = k % g.Q, pp = (k / g.Q) % g.P, n = k / (g.Q * g.P);
-    const int c = mn % g.C, rs = mn / g.C, s = rs % g.S, r = rs / g.S;
-    const int h = pp * g.stride - g.pad + r, w = q * g.stride - g.pad + s;
-    valid = h >= 0 && h < g.H && w >= 0 && w < g.W;
-    return valid ? p + (((long long)(n * g.H + h) * g.W + w) * g.C + c) * ES : p;
-  }
-}
-
-// Fill one operand tile of one stage.  ROWS = tile extent along mn (128 for A, BN for B).
-// `k0` = first reduction index of the stage, `k_end` = end of this split's range.
+// ---- operand gathers ---------------------------------------------------------------------------
+// One producer thread always works on the same tile row (K-major kinds) or the same 16-byte
+// mn-chunk (MN-major kinds), so everything that depends on it -- pixel (n,p,q) or filter tap
+// (r,s,c) -- is decoded ONCE in init(); per chunk only the reduction index is decoded, with
+// multiply-high divisions.  ROWS = tile extent along mn (128 for A, BN for B); ES = element bytes.
 template <int KIND, int ES, int ROWS>
-__device__ __forceinline__ void load_tile(uint32_t stage_smem, const void* base, long long ld, const Geom& g, int mn0,
-                                          int mn_limit, int k0, int k_end, int t) {
-  constexpr int T = 16 / ES;                  // elements per 16-byte chunk
-  constexpr int KELEMS = ROW_BYTES / ES;      // reduction elements per stage (32 fp32 / 64 bf16)
-  constexpr int CHUNKS = ROWS * 8;            // 16-byte chunks per stage
-  if (!is_mn(KIND)) {
-    // K-major canonical layout: chunk (row, kc) at kc*(ROWS*16) + (row/8)*128 + (row%8)*16
-    for (int idx = t; idx < CHUNKS; idx += PRODUCERS) {
-      const int row = idx % ROWS, kc = idx / ROWS;
-      bool valid;
-      const char* src = chunk_src<KIND, ES>(base, ld, g, mn0 + row, k0 + kc * T, mn_limit, k_end, valid);
-      cp_async16(stage_smem + kc * (ROWS * 16) + (row >> 3) * 128 + (row & 7) * 16, src, valid);
+struct TileLoader {
+  static constexpr int T = 16 / ES;                       // elements per 16-byte chunk
+  static constexpr int MNC = ROWS / T;                    // mn chunks per tile row (MN-major)
+  static constexpr int PER = ROWS * 8 / PRODUCERS;        // chunks per thread per stage
+  // K-major : 8 consecutive lanes read the 8 chunks (128 contiguous bytes) of one tile row, a thread
+  //           keeps its chunk column kc = t%8 and owns rows t/8 + 32*i        -> 4 lines per warp load
+  // MN-major: consecutive lanes read consecutive mn chunks of one k row, a thread keeps its mn chunk
+  //           and owns k rows kfirst + KSTEP*i                                -> 1-4 lines per warp load
+  static constexpr int KSTEP = PRODUCERS / MNC;
+  static_assert(PER >= 1 && ROWS * 8 % PRODUCERS == 0, "tile too small for the producer count");
+
+  const char* base;
+  long long ld;
+  int kc;                    // K-major: fixed 16-byte chunk column
+  int slot, kfirst;          // MN-major: fixed mn chunk, first k row
+  int mn[PER];
+  bool ok[PER];
+  int d0[PER], d1[PER], d2[PER];   // decoded row context (see init)
+
+  __device__ __forceinline__ void init(const void* base_, long long ld_, const Geom& g, int mn0, int mn_limit, int t) {
+    base = static_cast<const char*>(base_);
+    ld = ld_;
+    kc = t & 7;
+    slot = t % MNC;
+    kfirst = t / MNC;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      mn[i] = is_mn(KIND) ? mn0 + slot * T : mn0 + (t >> 3) + i * (PRODUCERS / 8);
+      ok[i] = mn[i] < mn_limit;
+      d0[i] = d1[i] = d2[i] = 0;
+      if (KIND == IM2COL_K) {               // d0 = image, d1 = p*stride - pad, d2 = q*stride - pad
+        int t1, q, pp;
+        g.fQ.divmod(mn[i], t1, q);
+        g.fP.divmod(t1, d0[i], pp);
+        d1[i] = pp * g.stride - g.pad;
+        d2[i] = q * g.stride - g.pad;
+      } else if (KIND == IM2COL_T_K) {      // d0 = image, d1 = h + pad, d2 = w + pad
+        int t1, w, h;
+        g.fW.divmod(mn[i], t1, w);
+        g.fH.divmod(t1, d0[i], h);
+        d1[i] = h + g.pad;
+        d2[i] = w + g.pad;
+      } else if (KIND == IM2COL_MN) {       // d0 = channel, d1 = r - pad, d2 = s - pad
+        int rs, r, sx;
+        g.fC.divmod(mn[i], rs, d0[i]);
+        g.fS.divmod(rs, r, sx);
+        d1[i] = r - g.pad;
+        d2[i] = sx - g.pad;
+      }
     }
-  } else {
-    constexpr int MNC = ROWS / T;
-    for (int idx = t; idx < CHUNKS; idx += PRODUCERS) {
-      const int mnc = idx % MNC, kk = idx / MNC;
-      if (kk >= KELEMS) break;
-      bool valid;
-      const char* src = chunk_src<KIND, ES>(base, ld, g, mn0 + mnc * T, k0 + kk, mn_limit, k_end, valid);
+  }
+
+  __device__ __forceinline__ void load(uint32_t stage_smem, const Geom& g, int k0, int k_end) const {
+    // K-major: the reduction index is the same for all of this thread's chunks -> decode once
+    int kr_s = 0, kr_c = 0, kr_r = 0, kr_sx = 0;
+    const int kk0 = k0 + kc * T;
+    if (KIND == IM2COL_K) {
+      g.fC.divmod(kk0, kr_s, kr_c);
+      g.fS.divmod(kr_s, kr_r, kr_sx);
+    } else if (KIND == IM2COL_T_K) {
+      g.fK.divmod(kk0, kr_s, kr_c);
+      g.fS.divmod(kr_s, kr_r, kr_sx);
+    }
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int kidx = kfirst + i * KSTEP;                // MN-major: k row of this chunk
+      const int k = is_mn(KIND) ? k0 + kidx : kk0;
+      bool valid = ok[i] && k < k_end;
+      const char* src = base;
+      if (valid) {
+        if (KIND == DENSE_K) {
+          src = base + ((long long)mn[i] * ld + k) * ES;
+        } else if (KIND == DENSE_MN) {
+          src = base + ((long long)k * ld + mn[i]) * ES;
+        } else if (KIND == IM2COL_K) {
+          const int h = d1[i] + kr_r, w = d2[i] + kr_sx;
+          valid = h >= 0 && h < g.H && w >= 0 && w < g.W;
+          if (valid) src = base + (((long long)(d0[i] * g.H + h) * g.W + w) * g.C + kr_c) * ES;
+        } else if (KIND == IM2COL_T_K) {
+          const int hh = d1[i] - kr_r, ww = d2[i] - kr_sx;
+          valid = hh >= 0 && ww >= 0;
+          if (valid) {
+            int pp, q, rh, rw;
+            g.fStride.divmod(hh, pp, rh);
+            g.fStride.divmod(ww, q, rw);
+            valid = rh == 0 && rw == 0 && pp < g.P && q < g.Q;
+            if (valid) src = base + (((long long)(d0[i] * g.P + pp) * g.Q + q) * g.K + kr_c) * ES;
+          }
+        } else if (KIND == WEIGHT_T_MN) {
+          int rs, co;
+          g.fK.divmod(k, rs, co);
+          src = base + (((long long)co * g.R * g.S + rs) * g.C + mn[i]) * ES;
+        } else {                          // IM2COL_MN: k = output pixel
+          int t1, q, nn, pp;
+          g.fQ.divmod(k, t1, q);
+          g.fP.divmod(t1, nn, pp);
+          const int h = pp * g.stride + d1[i], w = q * g.stride + d2[i];
+          valid = h >= 0 && h < g.H && w >= 0 && w < g.W;
+          if (valid) src = base + (((long long)(nn * g.H + h) * g.W + w) * g.C + d0[i]) * ES;
+        }
+      }
       uint32_t off;
-      if (ES == 2) {
-        // 16-bit MN-major, no swizzle: chunk (mnc, k) at (k/8)*((ROWS/T)*128) + mnc*128 + (k%8)*16
-        off = (kk >> 3) * (MNC * 128) + mnc * 128 + (kk & 7) * 16;
+      if (!is_mn(KIND)) {
+        // K-major SWIZZLE_128B: a tile row is 128 contiguous bytes, 8 rows form a 1024-byte atom,
+        // the 16-byte chunk index is XOR-ed with (row % 8) (address bits [4,7) ^= [7,10))
+        const int row = (int)(threadIdx.x >> 3) + i * (PRODUCERS / 8);
+        off = (row >> 3) * 1024 + (row & 7) * 128 + ((kc ^ (row & 7)) << 4);
+      } else if (ES == 2) {
+        // 16-bit MN-major, no swizzle: chunk (mnc, k) at (k/8)*(MNC*128) + mnc*128 + (k%8)*16
+        off = (kidx >> 3) * (MNC * 128) + slot * 128 + (kidx & 7) * 16;
       } else {
         // 32-bit MN-major exists only as SWIZZLE_128B_BASE32B: atom = 32 mn (one 128-byte row) x 4 k
         // rows; inside a row the 32-byte units are XOR-ed with the row index (byte-address bits
         // [5,7) ^= [7,9)).  Atoms tile MN first (512 B apart), then K.  (Layout measured on B200.)
-        const int c = mnc & 7, kr = kk & 3;
-        off = (mnc >> 3) * 512 + (kk >> 2) * ((ROWS / 32) * 512) + kr * 128 + ((((c >> 1) ^ kr) << 5) | ((c & 1) << 4));
+        const int c = slot & 7, kr = kidx & 3;
+        off = (slot >> 3) * 512 + (kidx >> 2) * ((ROWS / 32) * 512) + kr * 128 + ((((c >> 1) ^ kr) << 5) | ((c & 1) << 4));
       }
       cp_async16(stage_smem + off, src, valid);
     }
   }
-}
+};
 
 template <int AK, int BK_, int BN, bool BF16>
 __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
@@ -276,13 +350,17 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
 
   if (warp < 8) {
     // ================= producers =================
+    TileLoader<AK, ES, BM> la;
+    TileLoader<BK_, ES, BN> lb;
+    la.init(a.a, a.lda, a.g, m0, a.M, t);
+    lb.init(a.b, a.ldb, a.g, n0, a.N, t);
     int issued = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1, a.error);
       const int k0 = k_begin + kb * KELEMS;
-      load_tile<AK, ES, BM>(smem_a + s * A_STAGE, a.a, a.lda, a.g, m0, a.M, k0, k_end, t);
-      load_tile<BK_, ES, BN>(smem_b + s * B_STAGE, a.b, a.ldb, a.g, n0, a.N, k0, k_end, t);
+      la.load(smem_a + s * A_STAGE, a.g, k0, k_end);
+      lb.load(smem_b + s * B_STAGE, a.g, k0, k_end);
       cp_async_commit();
       ++issued;
       if (issued >= STAGES - 1) {
@@ -300,23 +378,27 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
   } else if ((t & 31) == 0) {
     // ================= MMA issuer (one thread) =================
     constexpr uint32_t idesc = make_idesc(BF16, is_mn(AK), is_mn(BK_), BN);
-    // canonical layouts: K-major no-swizzle (LBO = k-chunk stride, SBO = 8-row-group stride);
+    // canonical layouts: K-major SWIZZLE_128B (SBO = 8-row atom stride, start address walks 32 B per MMA);
     // bf16 MN-major no-swizzle (LBO = 8-k-group stride, SBO = mn-chunk stride);
     // fp32 MN-major 128B_BASE32B (LBO = mn-atom stride, SBO = 4-k-atom stride).
+    // layout type: K-major -> SWIZZLE_128B (2); fp32 MN-major -> 128B_BASE32B (1); bf16 MN-major -> none (0)
     constexpr bool A_SW = !BF16 && is_mn(AK), B_SW = !BF16 && is_mn(BK_);
-    constexpr uint32_t A_LBO = A_SW ? 512 : (is_mn(AK) ? (BM / T) * 128 : BM * 16);
-    constexpr uint32_t B_LBO = B_SW ? 512 : (is_mn(BK_) ? (BN / T) * 128 : BN * 16);
-    constexpr uint32_t A_SBO = A_SW ? (BM / 32) * 512 : 128, B_SBO = B_SW ? (BN / 32) * 512 : 128;
-    constexpr uint32_t A_STEP = A_SW ? 2 * A_SBO : (is_mn(AK) ? (UMMA_K / 8) * A_LBO : 2 * A_LBO);
-    constexpr uint32_t B_STEP = B_SW ? 2 * B_SBO : (is_mn(BK_) ? (UMMA_K / 8) * B_LBO : 2 * B_LBO);
+    constexpr uint32_t A_TYPE = !is_mn(AK) ? 2u : (A_SW ? 1u : 0u), B_TYPE = !is_mn(BK_) ? 2u : (B_SW ? 1u : 0u);
+    constexpr uint32_t A_LBO = !is_mn(AK) ? 16 : (A_SW ? 512 : (BM / T) * 128);
+    constexpr uint32_t B_LBO = !is_mn(BK_) ? 16 : (B_SW ? 512 : (BN / T) * 128);
+    constexpr uint32_t A_SBO = !is_mn(AK) ? 1024 : (A_SW ? (BM / 32) * 512 : 128);
+    constexpr uint32_t B_SBO = !is_mn(BK_) ? 1024 : (B_SW ? (BN / 32) * 512 : 128);
+    // start-address advance per MMA (K = 32 bytes of reduction)
+    constexpr uint32_t A_STEP = !is_mn(AK) ? 32 : (A_SW ? 2 * A_SBO : (UMMA_K / 8) * A_LBO);
+    constexpr uint32_t B_STEP = !is_mn(BK_) ? 32 : (B_SW ? 2 * B_SBO : (UMMA_K / 8) * B_LBO);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       mbar_wait(&full_bar[s], (kb / STAGES) & 1, a.error);
       tc_fence_after();
 #pragma unroll
       for (int j = 0; j < KELEMS / UMMA_K; ++j) {
-        const uint64_t da = make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_SW ? 1u : 0u);
-        const uint64_t db = make_desc(smem_b + s * B_STAGE + j * B_STEP, B_LBO, B_SBO, B_SW ? 1u : 0u);
+        const uint64_t da = make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
+        const uint64_t db = make_desc(smem_b + s * B_STAGE + j * B_STEP, B_LBO, B_SBO, B_TYPE);
         umma<BF16>(tmem_d, da, db, idesc, (kb | j) ? 1u : 0u);
       }
       umma_commit(&empty_bar[s]);          // frees the stage when these MMAs have read it
@@ -378,39 +460,70 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
     if (writer) {
       const int grow = m0 + row;
       const bool row_ok = grow < a.M;
-      float rsum = 0.f, rsq = 0.f;
+      if (a.transpose_out) {
+        // swapped orientation: rows are output channels, lanes walk consecutive channels, so the
+        // stores of one accumulator column are already coalesced (out[col * ldo + row])
+        float rsum = 0.f, rsq = 0.f;
+        const float bias = (a.bias != nullptr && row_ok) ? __ldg(a.bias + grow) : 0.f;
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        if (!(COLS_PER_WARP >= 16 || col_half == 0)) continue;
+        for (int c = 0; c < NCH; ++c)
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int col = col_base + c * 16 + j;
-          const int gcol = n0 + col;
-          const bool ok = row_ok && col < BN && gcol < a.N;
-          float v = acc[c][j];
-          if (a.bias != nullptr && ok) v += __ldg(a.bias + (a.transpose_out ? grow : gcol));
-          if (ok) {
-            float* dst = a.transpose_out ? a.out + (size_t)gcol * a.ldo + grow : a.out + (size_t)grow * a.ldo + gcol;
-            *dst = a.accumulate ? *dst + v : v;
+          for (int j = 0; j < 16; ++j) {
+            const int gcol = n0 + col_base + c * 16 + j;
+            if (row_ok && gcol < a.N) {
+              const float v = acc[c][j] + bias;
+              float* dst = a.out + (size_t)gcol * a.ldo + grow;
+              *dst = a.accumulate ? *dst + v : v;
+              rsum += v;
+              rsq += v * v;
+            }
           }
-          if (a.stats != nullptr) {
-            const float u = ok ? v : 0.f;
-            if (a.transpose_out) {            // channel == row: accumulate along this thread's columns
-              rsum += u;
-              rsq += u * u;
-            } else {                          // channel == column: reduce over the warp's 32 rows
-              const float cs = warp_sum(u), cq = warp_sum(u * u);
-              if ((t & 31) == 0 && col < BN && gcol < a.N) {
-                atomicAdd(a.stats + gcol, cs);
-                atomicAdd(a.stats + a.N + gcol, cq);
-              }
+        if (a.stats != nullptr && row_ok) {
+          atomicAdd(a.stats + grow, rsum);
+          atomicAdd(a.stats + a.M + grow, rsq);
+        }
+      } else {
+        // row-major output: stage the tile through (now idle) pipeline smem so that global stores
+        // are 128-byte row segments and the BatchNorm column sums come from conflict-free smem reads
+        float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
+        constexpr int LDS = BN + 1;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c)
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int col = col_base + c * 16 + j;
+            const int gcol = n0 + col;
+            float v = acc[c][j];
+            if (a.bias != nullptr && gcol < a.N) v += __ldg(a.bias + gcol);
+            stage[row * LDS + col] = v;
+          }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int lane = t & 31;
+#pragma unroll 4
+        for (int rr = 0; rr < BM / 8; ++rr) {
+          const int r = warp * (BM / 8) + rr, gr = m0 + r;
+          if (gr >= a.M) break;
+#pragma unroll
+          for (int col = lane; col < BN; col += 32) {
+            const int gc = n0 + col;
+            if (gc < a.N) {
+              float* dst = a.out + (size_t)gr * a.ldo + gc;
+              const float v = stage[r * LDS + col];
+              *dst = a.accumulate ? *dst + v : v;
             }
           }
         }
-      }
-      if (a.stats != nullptr && a.transpose_out && row_ok) {
-        atomicAdd(a.stats + grow, rsum);
-        atomicAdd(a.stats + a.M + grow, rsq);
+        if (a.stats != nullptr && t < BN && n0 + t < a.N) {
+          const int rows = min(BM, a.M - m0);
+          float cs = 0.f, cq = 0.f;
+          for (int r = 0; r < rows; ++r) {
+            const float v = stage[r * LDS + t];
+            cs += v;
+            cq += v * v;
+          }
+          atomicAdd(a.stats + n0 + t, cs);
+          atomicAdd(a.stats + a.N + n0 + t, cq);
+        }
       }
     }
   }
@@ -443,7 +556,10 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   const int k_blocks = ceil_div(a.Kd, KELEMS);
   int splits = 1;
   if (tiles < kNumSMs && a.workspace && a.counters && tiles <= max_counters && k_blocks >= 4) {
-    splits = min(min(kNumSMs / tiles, k_blocks / 2), 32);
+    // The tensor core eats a k-block in ~0.15 us, so unlike the FFMA path there is little to gain from
+    // slicing K finely, and every split costs a parked tile plus a serial reduction by the last CTA:
+    // split only so that no CTA runs more than ~24 k-blocks.
+    splits = min(min(ceil_div(k_blocks, 24), kNumSMs / tiles), 16);
     const size_t per_split = (size_t)tiles * BM * bn * sizeof(float);
     if ((size_t)splits * per_split > workspace_bytes) splits = (int)(workspace_bytes / per_split);
     splits = max(splits, 1);
@@ -503,6 +619,8 @@ static Geom make_geom(int Nb, int H, int W, int C, int K, int R, int S, int stri
   g.Nb = Nb; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.pad = pad;
   g.P = (H + 2 * pad - R) / stride + 1;
   g.Q = (W + 2 * pad - S) / stride + 1;
+  g.fQ = make_fastdiv(g.Q); g.fP = make_fastdiv(g.P); g.fC = make_fastdiv(C); g.fS = make_fastdiv(S);
+  g.fW = make_fastdiv(W); g.fH = make_fastdiv(H); g.fK = make_fastdiv(K); g.fStride = make_fastdiv(stride);
   return g;
 }
 

@@ -111,41 +111,88 @@ def _ws_args(dev: torch.device):
 # ---------------------------------------------------------------------------------------
 import os as _os
 
-_tensor_cores = _os.environ.get("B200DDP_TC", "1") != "0"
+_tc_mode = _os.environ.get("B200DDP_TC", "auto")       # auto | 1 (always tcgen05) | 0 (always FFMA)
 _NOT_SUPPORTED = 801          # cudaErrorNotSupported: shape needs the FFMA fallback
 tc_launches = 0
 ffma_launches = 0
+_choice: Dict[tuple, bool] = {}       # (entry point, geometry) -> use tcgen05?
 
 
-def set_tensor_cores(enabled: bool) -> None:
-    """Route convolutions / linears through the tcgen05 kernels (TF32 math) when True."""
-    global _tensor_cores
-    _tensor_cores = bool(enabled)
+def set_tensor_cores(enabled) -> None:
+    """True: always the tcgen05 kernels; False: always the FFMA kernels; "auto": time both the
+    first time a shape is seen (outside graph capture) and keep the faster one."""
+    global _tc_mode
+    _tc_mode = "auto" if enabled == "auto" else ("1" if enabled else "0")
 
 
 def tensor_cores_enabled() -> bool:
-    return _tensor_cores
+    return _tc_mode != "0"
+
+
+def conv_choices() -> Dict[tuple, bool]:
+    return dict(_choice)
+
+
+def _launch_tc(name, head, geom, dev) -> int:
+    s = scratch(dev)
+    return getattr(load_library(), name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+
+
+def _launch_ffma(name, head, geom, dev) -> int:
+    lib = load_library()
+    if name == "b200_conv2d_fprop":
+        x, w, y, stats = head
+        return lib.b200_conv2d_fprop(x, w, _ptr(None), y, stats, *geom, *_ws_args(dev), _stream())
+    return getattr(lib, name)(*head, *geom, *_ws_args(dev), _stream())
+
+
+def _time_variant(fn, iters: int = 3) -> float:
+    fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / iters
 
 
 def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device) -> None:
-    """Try `<name>_tc` (tcgen05) first, fall back to the FFMA kernel for unsupported shapes."""
+    """Dispatch one convolution pass to the tcgen05 kernel or to the FFMA kernel."""
     global _launches, tc_launches, ffma_launches
-    if _tensor_cores:
-        lib = load_library()
-        s = scratch(dev)
-        rc = getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+    use_tc = _tc_mode == "1"
+    if _tc_mode == "auto":
+        key = (name,) + tuple(g.value for g in geom)
+        use_tc = _choice.get(key)
+        if use_tc is None:
+            if torch.cuda.is_current_stream_capturing():
+                use_tc = False                       # cannot time inside a capture: stay on the safe path
+            else:
+                # time both on the real operands; statistics / accumulation are switched off while
+                # timing so the repeated runs have no side effects beyond rewriting the output
+                quiet = head[:3] + (_ptr(None),) if name == "b200_conv2d_fprop" else head
+                if name == "b200_conv2d_wgrad":
+                    quiet = head[:3] + (_i(0),)
+                if _launch_tc(name, quiet, geom, dev) == 0:
+                    t_tc = _time_variant(lambda: _launch_tc(name, quiet, geom, dev))
+                    t_ff = _time_variant(lambda: _launch_ffma(name, quiet, geom, dev))
+                    use_tc = t_tc < t_ff
+                else:
+                    use_tc = False
+                _choice[key] = use_tc
+    if use_tc:
+        rc = _launch_tc(name, head, geom, dev)
         if rc == 0:
             _launches += 1
             tc_launches += 1
             return
         if rc != _NOT_SUPPORTED:
             raise RuntimeError(f"{name}_tc failed: CUDA error {rc}")
+    rc = _launch_ffma(name, head, geom, dev)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed: CUDA error {rc}")
+    _launches += 1
     ffma_launches += 1
-    if name == "b200_conv2d_fprop":
-        x, w, y, stats = head
-        _call(name, x, w, _ptr(None), y, stats, *geom, *_ws_args(dev), _stream())
-    else:
-        _call(name, *head, *geom, *_ws_args(dev), _stream())
 
 
 def tc_error_word(device=None) -> int:

@@ -17,7 +17,7 @@ def nat():
     torch.backends.cuda.matmul.allow_tf32 = False
     native.set_tensor_cores(False)       # this module checks the exact-fp32 FFMA kernels
     yield native
-    native.set_tensor_cores(True)
+    native.set_tensor_cores("auto")
 
 
 def _cl(t):

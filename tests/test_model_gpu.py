@@ -20,8 +20,9 @@ def _library_math_like_the_reference():
     d.ops.set_native(True)
     from distributeddataparallel_b200.ops import native
 
-    native.set_tensor_cores(True)
+    native.set_tensor_cores(True)        # every eligible conv on the tcgen05 kernels
     yield
+    native.set_tensor_cores("auto")
     d.ops.set_native(True)
 
 

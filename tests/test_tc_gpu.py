@@ -12,7 +12,8 @@ def nat():
     from distributeddataparallel_b200.ops import native
 
     native.load_library()
-    return native
+    yield native
+    native.set_tensor_cores("auto")
 
 
 def _rel(a, b):
