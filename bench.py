@@ -93,10 +93,24 @@ def barrier(world):
     torch.cuda.synchronize()
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner, the reference's loss prints) write to fd 1; the contract is
+    ONE JSON line on stdout, so everything else is routed to stderr for the duration of the run."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
 def emit(rank, payload):
     if rank == 0:
-        sys.stdout.write(json.dumps(payload) + "\n")
-        sys.stdout.flush()
+        out = _REAL_STDOUT or sys.stdout
+        out.write(json.dumps(payload) + "\n")
+        out.flush()
 
 
 # =========================================================================================
@@ -302,6 +316,15 @@ def run_reference(args, rank, local_rank, world):
                 yield next(it)
             torch.cuda.synchronize()
             marks["b_t1"] = time.perf_counter()
+            # the reference's process group is still up here (dpp.cleanup runs after the loop):
+            # reduce the two timings to their max over ranks now
+            a_ms = marks["a0"].elapsed_time(marks["a1"])
+            b_ms = (marks["b_t1"] - marks["b_t0"]) * 1e3
+            if world > 1:
+                t = torch.tensor([a_ms, b_ms], dtype=torch.float64, device=torch.device("cuda", local_rank))
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                a_ms, b_ms = float(t[0]), float(t[1])
+            marks["a_ms"], marks["b_ms"] = a_ms, b_ms
 
     dpp.datasets = _Datasets
     dpp.models = _Models
@@ -309,15 +332,7 @@ def run_reference(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     with contextlib.redirect_stdout(sys.stderr):
         dpp.train(rank, world, epochs=1)          # the reference's own public per-rank API
-    dev = torch.device("cuda", local_rank)
-    # process group is gone (dpp.cleanup); use a fresh one only to take the max over ranks
-    a_ms = marks["a0"].elapsed_time(marks["a1"])
-    b_ms = (marks["b_t1"] - marks["b_t0"]) * 1e3
-    if world > 1:
-        dist.init_process_group("nccl", rank=rank, world_size=world)
-        a_ms = max_over_ranks(a_ms, world, dev)
-        b_ms = max_over_ranks(b_ms, world, dev)
-        dist.destroy_process_group()
+    a_ms, b_ms = marks["a_ms"], marks["b_ms"]
     samples = K * B * world
     clocks = marks.get("clocks", {})
     emit(rank, {
@@ -341,6 +356,7 @@ def run_reference(args, rank, local_rank, world):
 def main():
     args = parse()
     rank, local_rank, world = dist_env(args)
+    quiet_stdout()
     if args.impl == "reference":
         try:
             run_reference(args, rank, local_rank, world)
