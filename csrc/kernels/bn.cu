@@ -196,6 +196,105 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
   }
 }
 
+// ---- backward, single launch: reduce -> grid barrier -> apply ------------------------------------
+// All blocks are co-resident (grid <= 120, one or more per SM), so after publishing its partial
+// sums a block may wait for the others on a ticket counter and then apply dx with the complete
+// sums.  Saves one launch per BatchNorm layer per step and keeps dy / x hot in L2 between phases.
+__global__ void __launch_bounds__(256) bn_bwd_fused_kernel(
+    const float* __restrict__ dy, const float* __restrict__ out, const float* __restrict__ x,
+    const float* __restrict__ gamma, const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+    float* __restrict__ sums, float* __restrict__ dx, float* __restrict__ dres, float* __restrict__ dgamma,
+    float* __restrict__ dbeta, int accumulate_param_grads, float* zero_after, int zero_count, unsigned* tickets,
+    int M, int C, int relu) {
+  __shared__ float sh[2048];
+  const int tid = threadIdx.x, lanes = blockDim.x;
+  const int c4n = C >> 2;
+  // ---- phase 1: partial sums (every block walks all channel chunks for its row stripe) ----
+  for (int cbase4 = 0; cbase4 < c4n; cbase4 += 256) {
+    const int cw = min(c4n - cbase4, 256);
+    for (int i = tid; i < 2048; i += lanes) sh[i] = 0.f;
+    __syncthreads();
+    const int rows_per_iter = max(1, lanes / cw);
+    const int my_l = tid % cw, my_r = tid / cw;
+    if (my_r < rows_per_iter) {
+      const int c = (cbase4 + my_l) * 4;
+      const float4 mu = ldg4(save_mean + c), is = ldg4(save_invstd + c);
+      float4 s = make_float4(0, 0, 0, 0), q = make_float4(0, 0, 0, 0);
+      for (int r = blockIdx.x * rows_per_iter + my_r; r < M; r += gridDim.x * rows_per_iter) {
+        const size_t off = (size_t)r * C + c;
+        float4 g = ldg4(dy + off);
+        if (relu) {
+          const float4 o = ldg4(out + off);
+          g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
+          g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+        }
+        const float4 v = ldg4(x + off);
+        s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+        q.x += g.x * (v.x - mu.x) * is.x; q.y += g.y * (v.y - mu.y) * is.y;
+        q.z += g.z * (v.z - mu.z) * is.z; q.w += g.w * (v.w - mu.w) * is.w;
+      }
+      atomicAdd(&sh[my_l * 4 + 0], s.x); atomicAdd(&sh[my_l * 4 + 1], s.y);
+      atomicAdd(&sh[my_l * 4 + 2], s.z); atomicAdd(&sh[my_l * 4 + 3], s.w);
+      atomicAdd(&sh[1024 + my_l * 4 + 0], q.x); atomicAdd(&sh[1024 + my_l * 4 + 1], q.y);
+      atomicAdd(&sh[1024 + my_l * 4 + 2], q.z); atomicAdd(&sh[1024 + my_l * 4 + 3], q.w);
+    }
+    __syncthreads();
+    for (int i = tid; i < cw * 4; i += lanes) {
+      atomicAdd(sums + cbase4 * 4 + i, sh[i]);
+      atomicAdd(sums + C + cbase4 * 4 + i, sh[1024 + i]);
+    }
+    __syncthreads();
+  }
+  // ---- grid barrier ----
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    atomicAdd(tickets, 1u);
+    unsigned seen, spins = 0;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(tickets) : "memory");
+    } while (seen < gridDim.x && ++spins < (1u << 28));
+  }
+  __syncthreads();
+  // ---- phase 2: apply ----
+  const float inv_m = 1.f / (float)M;
+  const size_t total4 = (size_t)M * C / 4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % c4n) * 4;
+    const float4 mu = ldg4(save_mean + c), is = ldg4(save_invstd + c), ga = ldg4(gamma + c);
+    const float4 sd = __ldcg(reinterpret_cast<const float4*>(sums + c));
+    const float4 sx = __ldcg(reinterpret_cast<const float4*>(sums + C + c));
+    float4 g = ldg4(dy + i * 4);
+    if (relu) {
+      const float4 o = ldg4(out + i * 4);
+      g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
+      g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+    }
+    if (dres != nullptr) st4(dres + i * 4, g);
+    const float4 v = ldg4(x + i * 4);
+    float4 d;
+    d.x = ga.x * is.x * (g.x - sd.x * inv_m - (v.x - mu.x) * is.x * sx.x * inv_m);
+    d.y = ga.y * is.y * (g.y - sd.y * inv_m - (v.y - mu.y) * is.y * sx.y * inv_m);
+    d.z = ga.z * is.z * (g.z - sd.z * inv_m - (v.z - mu.z) * is.z * sx.z * inv_m);
+    d.w = ga.w * is.w * (g.w - sd.w * inv_m - (v.w - mu.w) * is.w * sx.w * inv_m);
+    st4(dx + i * 4, d);
+  }
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const float sb = __ldcg(sums + c), sg = __ldcg(sums + C + c);
+      if (accumulate_param_grads) { dbeta[c] += sb; dgamma[c] += sg; }
+      else { dbeta[c] = sb; dgamma[c] = sg; }
+    }
+    for (int i = threadIdx.x; i < zero_count; i += blockDim.x) zero_after[i] = 0.f;
+  }
+  // last block to leave re-arms the barrier
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned left = atomicAdd(tickets + 1, 1u);
+    if (left == gridDim.x - 1) { tickets[0] = 0u; tickets[1] = 0u; }
+  }
+}
+
 static int grid_for(size_t work_items, int per_block, int cap) {
   size_t g = (work_items + per_block - 1) / per_block;
   if (g < 1) g = 1;
@@ -248,5 +347,18 @@ B200_API int b200_bn_bwd_apply(const float* dy, const float* out, const float* x
   const int grid = grid_for((size_t)M * C / 4, 256 * 2, 4 * kNumSMs);
   bn_bwd_apply_kernel<<<grid, 256, 0, stream>>>(dy, out, x, gamma, save_mean, save_invstd, sums, dx, dres, dgamma,
                                                 dbeta, accumulate_param_grads, zero_after, zero_count, M, C, relu);
+  B200_LAUNCH_CHECK();
+}
+
+B200_API int b200_bn_bwd_fused(const float* dy, const float* out, const float* x, const float* gamma,
+                               const float* save_mean, const float* save_invstd, float* sums, float* dx, float* dres,
+                               float* dgamma, float* dbeta, int accumulate_param_grads, float* zero_after,
+                               int zero_count, unsigned* tickets, int M, int C, int relu, cudaStream_t stream) {
+  if (C % 4 != 0) return static_cast<int>(cudaErrorInvalidValue);
+  // all blocks must be resident at once (they wait for each other): <= 120 blocks of 256 threads
+  const int grid = grid_for((size_t)M * C / 4, 256 * 2, 120);
+  bn_bwd_fused_kernel<<<grid, 256, 0, stream>>>(dy, out, x, gamma, save_mean, save_invstd, sums, dx, dres, dgamma,
+                                                dbeta, accumulate_param_grads, zero_after, zero_count, tickets, M, C,
+                                                relu);
   B200_LAUNCH_CHECK();
 }

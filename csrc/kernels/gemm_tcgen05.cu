@@ -425,37 +425,109 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
         tmem_ld16(tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(col_base + c * 16), acc[c]);
     }
     if (a.splits > 1) {
+      // ---- split-K: park the partial tile, then ALL splits of this tile reduce it together ----
+      // Every split CTA sums one slice of rows over all parked partials and writes that slice of
+      // the output, so the reduction cost per CTA is one tile of reads no matter how many splits
+      // there are (a lone "last CTA reduces everything" step would serialise splits x 64 KB).
+      // Needs the splits of a tile co-resident: the host keeps tiles*splits <= 128 CTAs (1 per SM).
       float* mine = a.workspace + ((size_t)blockIdx.z * tiles + tile_id) * (BM * BN);
 #pragma unroll
       for (int c = 0; c < NCH; ++c)
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int col = col_base + c * 16 + j;
-          if (col < BN && (COLS_PER_WARP >= 16 || col_half == 0)) mine[(size_t)col * BM + row] = acc[c][j];
-        }
+        for (int j = 0; j < 16; ++j) mine[(size_t)(col_base + c * 16 + j) * BM + row] = acc[c][j];
       __threadfence();
-      asm volatile("bar.sync 1, 256;" ::: "memory");           // producers/epilogue warps only
-      if (t == 0) ticket_s = atomicAdd(&a.counters[tile_id], 1u);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      writer = ticket_s == (unsigned)(a.splits - 1);
-      if (writer) {
-        __threadfence();
-#pragma unroll
-        for (int c = 0; c < NCH; ++c)
-#pragma unroll
-          for (int j = 0; j < 16; ++j) acc[c][j] = 0.f;
-        for (int s = 0; s < a.splits; ++s) {
-          const float* part = a.workspace + ((size_t)s * tiles + tile_id) * (BM * BN);
-#pragma unroll
-          for (int c = 0; c < NCH; ++c)
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int col = col_base + c * 16 + j;
-              if (col < BN && (COLS_PER_WARP >= 16 || col_half == 0)) acc[c][j] += __ldcg(part + (size_t)col * BM + row);
-            }
-        }
-        if (t == 0) a.counters[tile_id] = 0u;
+      asm volatile("bar.sync 1, 256;" ::: "memory");           // producer/epilogue warps only
+      unsigned* arrive = a.counters + 2 * tile_id;
+      if (t == 0) {
+        atomicAdd(arrive, 1u);
+        unsigned spins = 0, seen;
+        do {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(arrive) : "memory");
+          if (++spins > kWaitLimit) {
+            if (a.error) atomicExch(a.error, 0xBAD05B17u);
+            break;
+          }
+        } while (seen < (unsigned)a.splits);
       }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const int rows_per = (BM + a.splits - 1) / a.splits;
+      const int r0 = blockIdx.z * rows_per;
+      const int nrows = max(0, min(BM, r0 + rows_per) - r0);
+      float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
+      constexpr int LDS = BN + 1;
+      const float* ws_tile = a.workspace + (size_t)tile_id * (BM * BN);
+      const size_t split_stride = (size_t)tiles * (BM * BN);
+      for (int idx = t; idx < nrows * BN; idx += PRODUCERS) {
+        const int rr = idx % nrows, col = idx / nrows;
+        const float* src = ws_tile + (size_t)col * BM + r0 + rr;
+        float v = 0.f;
+        for (int sp = 0; sp < a.splits; ++sp) v += __ldcg(src + sp * split_stride);
+        stage[rr * LDS + col] = v;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const int lane = t & 31;
+      if (!a.transpose_out) {
+        for (int rr = warp; rr < nrows; rr += 8) {
+          const int gr = m0 + r0 + rr;
+          if (gr >= a.M) break;
+          for (int col = lane; col < BN; col += 32) {
+            const int gc = n0 + col;
+            if (gc < a.N) {
+              float v = stage[rr * LDS + col];
+              if (a.bias != nullptr) v += __ldg(a.bias + gc);
+              float* dst = a.out + (size_t)gr * a.ldo + gc;
+              *dst = a.accumulate ? *dst + v : v;
+            }
+          }
+        }
+        if (a.stats != nullptr && t < BN && n0 + t < a.N) {
+          const int rows = min(nrows, a.M - m0 - r0);
+          float cs = 0.f, cq = 0.f;
+          const float bias = a.bias != nullptr ? __ldg(a.bias + n0 + t) : 0.f;
+          for (int rr = 0; rr < rows; ++rr) {
+            const float v = stage[rr * LDS + t] + bias;
+            cs += v;
+            cq += v * v;
+          }
+          if (rows > 0) {
+            atomicAdd(a.stats + n0 + t, cs);
+            atomicAdd(a.stats + a.N + n0 + t, cq);
+          }
+        }
+      } else {
+        for (int idx = t; idx < nrows * BN; idx += PRODUCERS) {
+          const int rr = idx % nrows, col = idx / nrows;
+          const int gr = m0 + r0 + rr, gc = n0 + col;
+          if (gr < a.M && gc < a.N) {
+            float v = stage[rr * LDS + col];
+            if (a.bias != nullptr) v += __ldg(a.bias + gr);
+            float* dst = a.out + (size_t)gc * a.ldo + gr;
+            *dst = a.accumulate ? *dst + v : v;
+          }
+        }
+        if (a.stats != nullptr && t < nrows && m0 + r0 + t < a.M) {
+          const int cols = min(BN, a.N - n0);
+          const float bias = a.bias != nullptr ? __ldg(a.bias + m0 + r0 + t) : 0.f;
+          float cs = 0.f, cq = 0.f;
+          for (int col = 0; col < cols; ++col) {
+            const float v = stage[t * LDS + col] + bias;
+            cs += v;
+            cq += v * v;
+          }
+          atomicAdd(a.stats + m0 + r0 + t, cs);
+          atomicAdd(a.stats + a.M + m0 + r0 + t, cq);
+        }
+      }
+      // the last split to leave re-arms the tile's counters for the next launch
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (t == 0) {
+        const unsigned left = atomicAdd(arrive + 1, 1u);
+        if (left == (unsigned)(a.splits - 1)) {
+          arrive[0] = 0u;
+          arrive[1] = 0u;
+        }
+      }
+      writer = false;
     }
     if (writer) {
       const int grow = m0 + row;
@@ -555,11 +627,11 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   const int tiles = tm * tn;
   const int k_blocks = ceil_div(a.Kd, KELEMS);
   int splits = 1;
-  if (tiles < kNumSMs && a.workspace && a.counters && tiles <= max_counters && k_blocks >= 4) {
-    // The tensor core eats a k-block in ~0.15 us, so unlike the FFMA path there is little to gain from
-    // slicing K finely, and every split costs a parked tile plus a serial reduction by the last CTA:
-    // split only so that no CTA runs more than ~24 k-blocks.
-    splits = min(min(ceil_div(k_blocks, 24), kNumSMs / tiles), 16);
+  if (tiles < 64 && a.workspace && a.counters && 2 * tiles <= max_counters && k_blocks >= 4) {
+    // One CTA keeps at most 3 stages (96 KB) of loads in flight, i.e. ~60-100 GB/s at DRAM/L2
+    // latency: streaming the operands fast needs MANY CTAs, so K is split until ~128 CTAs run
+    // (all co-resident, one per SM: the splits of a tile wait for each other in the epilogue).
+    splits = min(min(128 / tiles, k_blocks / 2), 32);
     const size_t per_split = (size_t)tiles * BM * bn * sizeof(float);
     if ((size_t)splits * per_split > workspace_bytes) splits = (int)(workspace_bytes / per_split);
     splits = max(splits, 1);

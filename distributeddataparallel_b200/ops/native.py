@@ -300,6 +300,9 @@ def conv2d(x, w, stride: int, padding: int, stats: Optional[torch.Tensor] = None
 # ---------------------------------------------------------------------------------------
 # batch norm (+ residual) (+ relu)
 # ---------------------------------------------------------------------------------------
+_FUSED_BN_BWD = _os.environ.get("B200DDP_FUSED_BN_BWD", "0") != "0"   # measured: no gain (step is not launch bound)
+
+
 class BNWorkspace:
     """Per-layer statistic accumulators.  ``fwd`` is filled by the producing conv's epilogue
     (or by bn_stats), ``bwd`` by bn_bwd_reduce; each apply kernel zeroes the *other* buffer so
@@ -308,6 +311,7 @@ class BNWorkspace:
     def __init__(self, channels: int, device) -> None:
         self.fwd = torch.zeros(2 * channels, dtype=torch.float32, device=device)
         self.bwd = torch.zeros(2 * channels, dtype=torch.float32, device=device)
+        self.tickets = torch.zeros(2, dtype=torch.int32, device=device)      # grid barrier of the fused backward
         self.fwd_dirty = False
         self.bwd_dirty = False
 
@@ -362,16 +366,21 @@ class _BatchNormAct(torch.autograd.Function):
             raise RuntimeError("backward through eval-mode BatchNorm is not supported by the native kernels")
         if ws.bwd_dirty:
             ws.bwd.zero_()
-        _call("b200_bn_bwd_reduce", _ptr(dout), _ptr(out), _ptr(xc), _ptr(save_mean), _ptr(save_invstd),
-              _ptr(ws.bwd), _i(m), _i(c), _i(int(relu)), _stream())
         ws.bwd_dirty = True
         dx = torch.empty_like(xc, memory_format=torch.preserve_format)
         dres = torch.empty_like(xc, memory_format=torch.preserve_format) if has_res else None
         dgamma, _ = _grad_target(ctx.params[0], ctx.slots[0], gamma)
         dbeta, _ = _grad_target(ctx.params[1], ctx.slots[1], gamma)
-        _call("b200_bn_bwd_apply", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean), _ptr(save_invstd),
-              _ptr(ws.bwd), _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0),
-              _ptr(ws.fwd), _i(ws.fwd.numel()), _i(m), _i(c), _i(int(relu)), _stream())
+        if _FUSED_BN_BWD:
+            _call("b200_bn_bwd_fused", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean),
+                  _ptr(save_invstd), _ptr(ws.bwd), _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0),
+                  _ptr(ws.fwd), _i(ws.fwd.numel()), _ptr(ws.tickets), _i(m), _i(c), _i(int(relu)), _stream())
+        else:
+            _call("b200_bn_bwd_reduce", _ptr(dout), _ptr(out), _ptr(xc), _ptr(save_mean), _ptr(save_invstd),
+                  _ptr(ws.bwd), _i(m), _i(c), _i(int(relu)), _stream())
+            _call("b200_bn_bwd_apply", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean),
+                  _ptr(save_invstd), _ptr(ws.bwd), _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0),
+                  _ptr(ws.fwd), _i(ws.fwd.numel()), _i(m), _i(c), _i(int(relu)), _stream())
         ws.fwd_dirty = False
         return dx, dgamma, dbeta, None, None, None, dres, None, None, None, None, None, None
 

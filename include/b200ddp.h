@@ -75,6 +75,12 @@ int b200_bn_bwd_apply(const float* dy, const float* out, const float* x, const f
                       float* dres, float* dgamma, float* dbeta, int accumulate_param_grads,
                       float* zero_after, int zero_count, int M, int C, int relu, cudaStream_t stream);
 
+/* reduce + apply in one launch (blocks meet on `tickets`, 2 zero-initialised words left at zero) */
+int b200_bn_bwd_fused(const float* dy, const float* out, const float* x, const float* gamma,
+                      const float* save_mean, const float* save_invstd, float* sums, float* dx, float* dres,
+                      float* dgamma, float* dbeta, int accumulate_param_grads, float* zero_after,
+                      int zero_count, unsigned* tickets, int M, int C, int relu, cudaStream_t stream);
+
 /* ---- pooling --------------------------------------------------------------- */
 int b200_maxpool3x3s2_fwd(const float* x, float* y, uint8_t* idx, int Nb, int H, int W, int C, cudaStream_t stream);
 int b200_maxpool3x3s2_bwd(const float* dy, const uint8_t* idx, float* dx, int Nb, int H, int W, int C,

@@ -106,8 +106,11 @@ def test_graph_step_matches_eager():
         # bits, and this net amplifies that; the bounds leave room for it (a wrong or missing
         # kernel in the captured graph shows up as O(1) differences)
         assert abs(le - lg) < 1e-3 * max(1.0, abs(le)), (k, le, lg)
-        worst = max(_rel(a, b) for a, b in zip(mg.parameters(), me.parameters()))
-        assert worst < 2e-3, (k, worst)
+        # compare the whole parameter vector: per-tensor ratios blow up on tensors that are still
+        # ~0 (BatchNorm biases a few steps after zero init), where last-bit noise is the signal
+        pg = torch.cat([p.detach().reshape(-1) for p in mg.parameters()])
+        pe = torch.cat([p.detach().reshape(-1) for p in me.parameters()])
+        assert _rel(pg, pe) < 1e-3, (k, _rel(pg, pe))
         for (n, a), (_, b) in zip(mg.named_buffers(), me.named_buffers()):
             assert torch.allclose(a.float(), b.float(), rtol=1e-2, atol=1e-4), n
     assert int(mg.module.model.bn1.num_batches_tracked) == 6
