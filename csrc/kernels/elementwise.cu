@@ -1,4 +1,6 @@
 // Small elementwise kernels: input pipeline, scaling, accumulation.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "b200ddp.h"
 
@@ -59,6 +61,25 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ a
   }
 }
 
+// bf16 variant of colsum (bias gradients of bf16 Linear layers)
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ out,
+                                                          int M, int N, int accumulate) {
+  const int n = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int r0 = threadIdx.x >> 5;
+  __shared__ float sh[8][33];
+  float s = 0.f;
+  if (n < N)
+    for (int m = r0; m < M; m += 8) s += __bfloat162float(a[(size_t)m * N + n]);
+  sh[r0][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (r0 == 0 && n < N) {
+    float tot = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) tot += sh[r][threadIdx.x & 31];
+    out[n] = __float2bfloat16_rn(accumulate ? __bfloat162float(out[n]) + tot : tot);
+  }
+}
+
 static int grid1d(size_t n, int per_thread = 4) {
   size_t g = (n + 256 * per_thread - 1) / (256 * per_thread);
   return (int)(g < 1 ? 1 : (g > 8 * kNumSMs ? 8 * kNumSMs : g));
@@ -86,5 +107,11 @@ B200_API int b200_add(const float* a, const float* b, float* out, size_t n, cuda
 
 B200_API int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream) {
   colsum_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(a, out, M, N, accumulate);
+  B200_LAUNCH_CHECK();
+}
+
+B200_API int b200_colsum_bf16(const void* a, void* out, int M, int N, int accumulate, cudaStream_t stream) {
+  colsum_bf16_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a),
+                                                          static_cast<__nv_bfloat16*>(out), M, N, accumulate);
   B200_LAUNCH_CHECK();
 }

@@ -97,7 +97,23 @@ struct Args {
   int accumulate;
   int transpose_out;           // out[col * ldo + row]
   unsigned* error;
+  int out_bf16, bias_bf16;     // output / bias element type (default fp32)
+  // batched GEMM (attention): blockIdx.z = batch index z, element offsets (z / inner) * s0 + (z % inner) * s1
+  int batch, inner;
+  long long a_s0, a_s1, b_s0, b_s1, o_s0, o_s1;
 };
+
+__device__ __forceinline__ void store_out(const Args& a, float* out, size_t idx, float v) {
+  if (a.out_bf16) {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + idx;
+    *o = __float2bfloat16_rn(a.accumulate ? __bfloat162float(*o) + v : v);
+  } else {
+    out[idx] = a.accumulate ? out[idx] + v : v;
+  }
+}
+__device__ __forceinline__ float load_bias(const Args& a, int i) {
+  return a.bias_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(a.bias)[i]) : __ldg(a.bias + i);
+}
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -329,7 +345,14 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
 
   const int t = threadIdx.x, warp = t >> 5;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-  const int k_begin = blockIdx.z * a.k_per_split;
+  const int zb = a.batch > 1 ? (int)blockIdx.z : 0;                 // batch index (no split-K when batched)
+  const int split_z = a.batch > 1 ? 0 : (int)blockIdx.z;
+  const long long zo = zb / a.inner, zi = zb % a.inner;
+  const char* a_base = static_cast<const char*>(a.a) + (zo * a.a_s0 + zi * a.a_s1) * ES;
+  const char* b_base = static_cast<const char*>(a.b) + (zo * a.b_s0 + zi * a.b_s1) * ES;
+  float* out_base = reinterpret_cast<float*>(reinterpret_cast<char*>(a.out) +
+                                             (zo * a.o_s0 + zi * a.o_s1) * (a.out_bf16 ? 2 : 4));
+  const int k_begin = split_z * a.k_per_split;
   const int k_end = min(a.Kd, k_begin + a.k_per_split);
   const int num_kb = (k_end - k_begin + KELEMS - 1) / KELEMS;
   const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + STAGES * A_STAGE;   // swizzle is address based
@@ -352,8 +375,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
     // ================= producers =================
     TileLoader<AK, ES, BM> la;
     TileLoader<BK_, ES, BN> lb;
-    la.init(a.a, a.lda, a.g, m0, a.M, t);
-    lb.init(a.b, a.ldb, a.g, n0, a.N, t);
+    la.init(a_base, a.lda, a.g, m0, a.M, t);
+    lb.init(b_base, a.ldb, a.g, n0, a.N, t);
     int issued = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
@@ -430,7 +453,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
       // the output, so the reduction cost per CTA is one tile of reads no matter how many splits
       // there are (a lone "last CTA reduces everything" step would serialise splits x 64 KB).
       // Needs the splits of a tile co-resident: the host keeps tiles*splits <= 128 CTAs (1 per SM).
-      float* mine = a.workspace + ((size_t)blockIdx.z * tiles + tile_id) * (BM * BN);
+      float* mine = a.workspace + ((size_t)split_z * tiles + tile_id) * (BM * BN);
 #pragma unroll
       for (int c = 0; c < NCH; ++c)
 #pragma unroll
@@ -451,7 +474,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const int rows_per = (BM + a.splits - 1) / a.splits;
-      const int r0 = blockIdx.z * rows_per;
+      const int r0 = split_z * rows_per;
       const int nrows = max(0, min(BM, r0 + rows_per) - r0);
       float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
       constexpr int LDS = BN + 1;
@@ -474,16 +497,15 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
             const int gc = n0 + col;
             if (gc < a.N) {
               float v = stage[rr * LDS + col];
-              if (a.bias != nullptr) v += __ldg(a.bias + gc);
-              float* dst = a.out + (size_t)gr * a.ldo + gc;
-              *dst = a.accumulate ? *dst + v : v;
+              if (a.bias != nullptr) v += load_bias(a, gc);
+              store_out(a, out_base, (size_t)gr * a.ldo + gc, v);
             }
           }
         }
         if (a.stats != nullptr && t < BN && n0 + t < a.N) {
           const int rows = min(nrows, a.M - m0 - r0);
           float cs = 0.f, cq = 0.f;
-          const float bias = a.bias != nullptr ? __ldg(a.bias + n0 + t) : 0.f;
+          const float bias = a.bias != nullptr ? load_bias(a, n0 + t) : 0.f;
           for (int rr = 0; rr < rows; ++rr) {
             const float v = stage[rr * LDS + t] + bias;
             cs += v;
@@ -500,14 +522,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
           const int gr = m0 + r0 + rr, gc = n0 + col;
           if (gr < a.M && gc < a.N) {
             float v = stage[rr * LDS + col];
-            if (a.bias != nullptr) v += __ldg(a.bias + gr);
-            float* dst = a.out + (size_t)gc * a.ldo + gr;
-            *dst = a.accumulate ? *dst + v : v;
+            if (a.bias != nullptr) v += load_bias(a, gr);
+            store_out(a, out_base, (size_t)gc * a.ldo + gr, v);
           }
         }
         if (a.stats != nullptr && t < nrows && m0 + r0 + t < a.M) {
           const int cols = min(BN, a.N - n0);
-          const float bias = a.bias != nullptr ? __ldg(a.bias + m0 + r0 + t) : 0.f;
+          const float bias = a.bias != nullptr ? load_bias(a, m0 + r0 + t) : 0.f;
           float cs = 0.f, cq = 0.f;
           for (int col = 0; col < cols; ++col) {
             const float v = stage[t * LDS + col] + bias;
@@ -536,7 +557,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
         // swapped orientation: rows are output channels, lanes walk consecutive channels, so the
         // stores of one accumulator column are already coalesced (out[col * ldo + row])
         float rsum = 0.f, rsq = 0.f;
-        const float bias = (a.bias != nullptr && row_ok) ? __ldg(a.bias + grow) : 0.f;
+        const float bias = (a.bias != nullptr && row_ok) ? load_bias(a, grow) : 0.f;
 #pragma unroll
         for (int c = 0; c < NCH; ++c)
 #pragma unroll
@@ -544,8 +565,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
             const int gcol = n0 + col_base + c * 16 + j;
             if (row_ok && gcol < a.N) {
               const float v = acc[c][j] + bias;
-              float* dst = a.out + (size_t)gcol * a.ldo + grow;
-              *dst = a.accumulate ? *dst + v : v;
+              store_out(a, out_base, (size_t)gcol * a.ldo + grow, v);
               rsum += v;
               rsq += v * v;
             }
@@ -566,7 +586,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
             const int col = col_base + c * 16 + j;
             const int gcol = n0 + col;
             float v = acc[c][j];
-            if (a.bias != nullptr && gcol < a.N) v += __ldg(a.bias + gcol);
+            if (a.bias != nullptr && gcol < a.N) v += load_bias(a, gcol);
             stage[row * LDS + col] = v;
           }
         asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -578,11 +598,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
 #pragma unroll
           for (int col = lane; col < BN; col += 32) {
             const int gc = n0 + col;
-            if (gc < a.N) {
-              float* dst = a.out + (size_t)gr * a.ldo + gc;
-              const float v = stage[r * LDS + col];
-              *dst = a.accumulate ? *dst + v : v;
-            }
+            if (gc < a.N) store_out(a, out_base, (size_t)gr * a.ldo + gc, stage[r * LDS + col]);
           }
         }
         if (a.stats != nullptr && t < BN && n0 + t < a.N) {
@@ -627,7 +643,9 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   const int tiles = tm * tn;
   const int k_blocks = ceil_div(a.Kd, KELEMS);
   int splits = 1;
-  if (tiles < 64 && a.workspace && a.counters && 2 * tiles <= max_counters && k_blocks >= 4) {
+  if (a.batch < 1) a.batch = 1;
+  if (a.inner < 1) a.inner = 1;
+  if (a.batch == 1 && tiles < 64 && a.workspace && a.counters && 2 * tiles <= max_counters && k_blocks >= 4) {
     // One CTA keeps at most 3 stages (96 KB) of loads in flight, i.e. ~60-100 GB/s at DRAM/L2
     // latency: streaming the operands fast needs MANY CTAs, so K is split until ~128 CTAs run
     // (all co-resident, one per SM: the splits of a tile wait for each other in the epilogue).
@@ -639,7 +657,7 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   const int kps = ceil_div(k_blocks, splits) * KELEMS;
   a.splits = ceil_div(a.Kd, kps);
   a.k_per_split = kps;
-  dim3 grid(tm, tn, a.splits);
+  dim3 grid(tm, tn, a.batch > 1 ? a.batch : a.splits);
   if (bn == 32) return launch<AK, BK_, 32, BF16>(a, grid, st);
   if (bn == 64) return launch<AK, BK_, 64, BF16>(a, grid, st);
   return launch<AK, BK_, 128, BF16>(a, grid, st);
@@ -653,37 +671,50 @@ using namespace b200::tc;
 
 static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Dense GEMM, fp32 (TF32 math) or bf16 inputs, fp32 output:
+// Dense (optionally batched) GEMM; inputs fp32 (TF32 math) or bf16, output fp32 or bf16:
 //   mode 0 (NT): out[M,N] = A[M,K]  * B[N,K]^T      (Linear forward:  x, W)
 //   mode 1 (NN): out[M,N] = A[M,K]  * B[K,N]        (Linear dgrad:    dy, W)
 //   mode 2 (TN): out[M,N] = A[K,M]^T * B[K,N]       (Linear wgrad:    dy^T, x)
-B200_API int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, int M, int N, int K, int mode,
-                          int bf16, int accumulate, float* workspace, size_t workspace_bytes, unsigned* counters,
-                          int max_counters, unsigned* error, cudaStream_t stream) {
+// desc = {lda, ldb, ldo, batch, inner, a_s0, a_s1, b_s0, b_s1, o_s0, o_s1} (elements); batch z addresses
+// operand X at X + (z / inner) * x_s0 + (z % inner) * x_s1.  Leading dimensions must keep 16-byte
+// alignment of every row (ld % 4 == 0 for fp32, % 8 for bf16).  flags: bit0 inputs bf16, bit1 output
+// bf16, bit2 bias bf16, bit3 accumulate into out.
+B200_API int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, int mode,
+                             int flags, const long long* desc, float* workspace, size_t workspace_bytes,
+                             unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream) {
+  const bool bf16 = flags & 1;
   const int vec = bf16 ? 8 : 4;
   if (!ptr16(A) || !ptr16(B) || M <= 0 || N <= 0 || K <= 0) return static_cast<int>(cudaErrorInvalidValue);
   Args a{};
-  a.a = A; a.b = B; a.out = out; a.bias = bias; a.M = M; a.N = N; a.Kd = K; a.ldo = N; a.accumulate = accumulate;
+  a.a = A; a.b = B; a.out = static_cast<float*>(out); a.bias = static_cast<const float*>(bias);
+  a.M = M; a.N = N; a.Kd = K;
+  a.lda = desc[0]; a.ldb = desc[1]; a.ldo = desc[2];
+  a.batch = (int)desc[3]; a.inner = (int)desc[4];
+  a.a_s0 = desc[5]; a.a_s1 = desc[6]; a.b_s0 = desc[7]; a.b_s1 = desc[8]; a.o_s0 = desc[9]; a.o_s1 = desc[10];
+  a.out_bf16 = (flags >> 1) & 1; a.bias_bf16 = (flags >> 2) & 1; a.accumulate = (flags >> 3) & 1;
   a.workspace = workspace; a.counters = counters; a.error = error;
-  if (mode == 0) {
-    if (K % vec) return static_cast<int>(cudaErrorInvalidValue);
-    a.lda = K; a.ldb = K;
-    return bf16 ? dispatch_bn<DENSE_K, DENSE_K, true>(a, workspace_bytes, max_counters, 0, stream)
-                : dispatch_bn<DENSE_K, DENSE_K, false>(a, workspace_bytes, max_counters, 0, stream);
-  }
-  if (mode == 1) {
-    if (K % vec || N % vec) return static_cast<int>(cudaErrorInvalidValue);
-    a.lda = K; a.ldb = N;
-    return bf16 ? dispatch_bn<DENSE_K, DENSE_MN, true>(a, workspace_bytes, max_counters, 0, stream)
-                : dispatch_bn<DENSE_K, DENSE_MN, false>(a, workspace_bytes, max_counters, 0, stream);
-  }
-  if (mode == 2) {
-    if (M % vec || N % vec) return static_cast<int>(cudaErrorInvalidValue);
-    a.lda = M; a.ldb = N;
-    return bf16 ? dispatch_bn<DENSE_MN, DENSE_MN, true>(a, workspace_bytes, max_counters, 0, stream)
-                : dispatch_bn<DENSE_MN, DENSE_MN, false>(a, workspace_bytes, max_counters, 0, stream);
-  }
+  if (a.lda % vec || a.ldb % vec) return static_cast<int>(cudaErrorInvalidValue);
+  if (a.a_s0 % vec || a.a_s1 % vec || a.b_s0 % vec || a.b_s1 % vec) return static_cast<int>(cudaErrorInvalidValue);
+#define B200_GEMM_MODE(AK, BKIND)                                                                    \
+  return bf16 ? dispatch_bn<AK, BKIND, true>(a, workspace_bytes, max_counters, 0, stream)            \
+              : dispatch_bn<AK, BKIND, false>(a, workspace_bytes, max_counters, 0, stream)
+  if (mode == 0) { B200_GEMM_MODE(DENSE_K, DENSE_K); }
+  if (mode == 1) { B200_GEMM_MODE(DENSE_K, DENSE_MN); }
+  if (mode == 2) { B200_GEMM_MODE(DENSE_MN, DENSE_MN); }
+#undef B200_GEMM_MODE
   return static_cast<int>(cudaErrorInvalidValue);
+}
+
+// Convenience form: contiguous operands, fp32 output.
+B200_API int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, int M, int N, int K, int mode,
+                          int bf16, int accumulate, float* workspace, size_t workspace_bytes, unsigned* counters,
+                          int max_counters, unsigned* error, cudaStream_t stream) {
+  long long desc[11] = {0, 0, N, 1, 1, 0, 0, 0, 0, 0, 0};
+  if (mode == 0) { desc[0] = K; desc[1] = K; }
+  else if (mode == 1) { desc[0] = K; desc[1] = N; }
+  else { desc[0] = M; desc[1] = N; }
+  return b200_gemm_tc_ex(A, B, out, bias, M, N, K, mode, (bf16 ? 1 : 0) | (accumulate ? 8 : 0), desc, workspace,
+                         workspace_bytes, counters, max_counters, error, stream);
 }
 
 static Geom make_geom(int Nb, int H, int W, int C, int K, int R, int S, int stride, int pad) {

@@ -7,6 +7,8 @@
 // table maps each CTA-sized chunk to (tensor, offset), so the launch geometry is fixed and
 // the kernel is CUDA-graph friendly.  Hyper-parameters are read from device memory (`hyper`)
 // so a captured graph follows learning-rate changes without re-capture.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 #include "b200ddp.h"
 
@@ -20,7 +22,7 @@ struct __align__(16) TensorRec {
   float* s0;      // SGD: momentum buffer   Adam: exp_avg
   float* s1;      // Adam: exp_avg_sq
   long long n;
-  long long pad;
+  long long dtype;   // 0: p/g fp32   1: p/g bf16 (optimizer state stays fp32)
 };
 
 struct ChunkRec { int tensor; int chunk; };
@@ -48,7 +50,15 @@ __global__ void __launch_bounds__(256) sgd_kernel(const TensorRec* __restrict__ 
     }
     return fmaf(-lr, g, p);
   };
-  if (vec && (end - base) % 4 == 0) {
+  if (r.dtype == 1) {
+    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(r.p);
+    const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(r.g);
+    for (long long i = base + threadIdx.x; i < end; i += 256) {
+      float b = r.s0 ? r.s0[i] : 0.f;
+      pb[i] = __float2bfloat16_rn(upd(__bfloat162float(pb[i]), __bfloat162float(gb[i]), b));
+      if (r.s0) r.s0[i] = b;
+    }
+  } else if (vec && (end - base) % 4 == 0) {
     for (long long i = base + threadIdx.x * 4; i < end; i += 256 * 4) {
       float4 p = *reinterpret_cast<const float4*>(r.p + i);
       const float4 g = *reinterpret_cast<const float4*>(r.g + i);
@@ -80,8 +90,11 @@ __global__ void __launch_bounds__(256) adam_kernel(const TensorRec* __restrict__
   const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
   const long long base = (long long)ch.chunk * kChunk;
   const long long end = min(r.n, base + kChunk);
+  const bool bf = r.dtype == 1;
+  __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(r.p);
+  const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(r.g);
   for (long long i = base + threadIdx.x; i < end; i += 256) {
-    float p = r.p[i], g = r.g[i] * gscale;
+    float p = bf ? __bfloat162float(pb[i]) : r.p[i], g = (bf ? __bfloat162float(gb[i]) : r.g[i]) * gscale;
     if (maximize) g = -g;
     if (wd != 0.f) {
       if (decoupled) p *= (1.f - lr * wd);
@@ -91,7 +104,9 @@ __global__ void __launch_bounds__(256) adam_kernel(const TensorRec* __restrict__
     const float v = fmaf(b2, r.s1[i], (1.f - b2) * g * g);
     r.s0[i] = m;
     r.s1[i] = v;
-    r.p[i] = p - step_size * m / (sqrtf(v) * inv_sqrt_bc2 + eps);
+    const float pn = p - step_size * m / (sqrtf(v) * inv_sqrt_bc2 + eps);
+    if (bf) pb[i] = __float2bfloat16_rn(pn);
+    else r.p[i] = pn;
   }
 }
 

@@ -38,11 +38,16 @@ class TrainStep:
         self.use_graph = bool(cuda_graph) and dev.type == "cuda"
         self._ddp = model if hasattr(model, "reducer") else None
 
+    def _forward_loss(self, data, target):
+        inner = getattr(self.model, "module", self.model)
+        if getattr(inner, "computes_loss", False):          # e.g. GPT-2: fused LM head + cross-entropy
+            return self.model(data, target)
+        return self.criterion(self.model(data), target)
+
     # -- eager ---------------------------------------------------------------------------
     def _eager(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         self.optimizer.zero_grad()
-        out = self.model(data)
-        loss = self.criterion(out, target)
+        loss = self._forward_loss(data, target)
         loss.backward()
         self.optimizer.step()
         self.eager_steps += 1
@@ -74,17 +79,16 @@ class TrainStep:
                 self._ddp.reducer.attach_hooks()
         try:
             with torch.cuda.graph(graph, stream=cap_stream):
-                out = self.model(static_x)
-                loss = self.criterion(out, static_y)
+                loss = self._forward_loss(static_x, static_y)
                 loss.backward()
                 self.optimizer.step()
                 # drop the autograd graph now: it keeps the capture-stream accumulator nodes alive
-                loss, out = loss.detach(), out.detach()
+                loss = loss.detach()
         finally:
             if self._ddp is not None:
                 self._ddp.reducer.attach_hooks()
         native.set_launches_per_capture(native.launch_count() - launches0)
-        entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach(), "out": out.detach()}
+        entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach()}
         return entry
 
     def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:

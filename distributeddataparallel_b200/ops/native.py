@@ -553,8 +553,11 @@ def _is_dense(t: torch.Tensor) -> bool:
 
 
 def _dense_same_layout(ts: Sequence[torch.Tensor]) -> bool:
+    """p and g share dtype (fp32 or bf16) and layout; optimizer state tensors are fp32, same layout."""
     s0 = ts[0]
-    return all(_is_dense(t) and t.stride() == s0.stride() and t.dtype == torch.float32 for t in ts)
+    if ts[0].dtype not in (torch.float32, torch.bfloat16) or ts[1].dtype != ts[0].dtype:
+        return False
+    return all(_is_dense(t) and t.stride() == s0.stride() for t in ts) and all(t.dtype == torch.float32 for t in ts[2:])
 
 
 class _OptimTable:
@@ -567,9 +570,9 @@ class _OptimTable:
         for ti, p in enumerate(ps):
             tensors = [p, gs[ti]] + ([s0s[ti]] if s0s else []) + ([s1s[ti]] if s1s else [])
             if not _dense_same_layout(tensors):
-                raise RuntimeError("fused optimizer needs dense fp32 tensors with identical strides")
+                raise RuntimeError("fused optimizer needs dense fp32/bf16 params+grads (fp32 state) with identical strides")
             recs += struct.pack("<QQQQqq", p.data_ptr(), gs[ti].data_ptr(), s0s[ti].data_ptr() if s0s else 0,
-                                s1s[ti].data_ptr() if s1s else 0, p.numel(), 0)
+                                s1s[ti].data_ptr() if s1s else 0, p.numel(), int(p.dtype == torch.bfloat16))
             for c in range(-(-p.numel() // chunk)):
                 chunks += struct.pack("<ii", ti, c)
         self.num_chunks = len(chunks) // 8

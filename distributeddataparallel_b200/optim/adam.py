@@ -35,8 +35,9 @@ class Adam(torch.optim.Adam):
                 st = self.state[p]
                 if len(st) == 0:
                     st["step"] = torch.zeros((), dtype=torch.float32, device=p.device if p.is_cuda else "cpu")
-                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
-                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    sdt = torch.float32 if p.is_cuda else p.dtype      # fused kernels keep fp32 state
+                    st["exp_avg"] = torch.zeros_like(p, dtype=sdt, memory_format=torch.preserve_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, dtype=sdt, memory_format=torch.preserve_format)
             b1, b2 = group["betas"]
             if self._native and ps[0].is_cuda and ops.native_enabled():
                 from ..ops import native

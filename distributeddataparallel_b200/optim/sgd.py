@@ -48,7 +48,7 @@ class SGD(torch.optim.SGD):
                     st = self.state[p]
                     if st.get("momentum_buffer") is None:
                         # torch initialises the buffer with the first gradient (no dampening)
-                        st["momentum_buffer"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                        st["momentum_buffer"] = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.preserve_format)
                         first = True
                     bufs.append(st["momentum_buffer"])
             native.fused_sgd(self._tables, gi, ps, [p.grad for p in ps], bufs, lr=group["lr"],

@@ -97,9 +97,10 @@ int b200_softmax_xent(const float* logits, const long long* target, float* loss,
 int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, float scale_host, cudaStream_t stream);
 int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
 int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream);
+int b200_colsum_bf16(const void* a, void* out, int M, int N, int accumulate, cudaStream_t stream);
 
 /* ---- fused multi-tensor optimizers (optim.SGD at REF:41,53) -------------------------
- * recs: device array of {float* p, g, s0, s1; int64 n; int64 pad}; chunks: device array of
+ * recs: device array of {float* p, g, s0, s1; int64 n; int64 dtype (0 fp32, 1 bf16 p/g)}; chunks: device array of
  * {int tensor, int chunk}; hyper: device floats (layout in csrc/kernels/optim.cu). */
 int b200_optim_chunk_elems(void);
 int b200_optim_rec_bytes(void);
@@ -116,6 +117,10 @@ int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float*
 int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, int M, int N, int K, int mode,
                  int bf16, int accumulate, float* workspace, size_t workspace_bytes, unsigned* counters,
                  int max_counters, unsigned* error, cudaStream_t stream);
+/* general form: explicit leading dimensions, batching (attention) and bf16 output; see the .cu */
+int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, int mode,
+                    int flags, const long long* desc, float* workspace, size_t workspace_bytes,
+                    unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
 int b200_conv2d_fprop_tc(const float* x, const float* w, float* y, float* stats, int Nb, int H, int W, int C,
                          int K, int R, int S, int stride, int pad, float* workspace, size_t workspace_bytes,
                          unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
@@ -126,6 +131,24 @@ int b200_conv2d_wgrad_tc(const float* dy, const float* x, float* dw, int accumul
                          int C, int K, int R, int S, int stride, int pad, float* workspace,
                          size_t workspace_bytes, unsigned* counters, int max_counters, unsigned* error,
                          cudaStream_t stream);
+
+/* ---- transformer blocks (GPT-2 configuration): fp32 math on fp32 / bf16 storage -------- */
+int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                       int M, int D, float eps, int is_bf16, cudaStream_t st);
+int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                       void* dx, float* dgamma_acc, float* dbeta_acc, int M, int D, int is_bf16, cudaStream_t st);
+int b200_cast_from_f32(const float* in, void* out, size_t n, int accumulate, int is_bf16, cudaStream_t st);
+int b200_gelu_fwd(const void* x, void* y, size_t n, int is_bf16, cudaStream_t st);
+int b200_gelu_bwd(const void* x, const void* dy, void* dx, size_t n, int is_bf16, cudaStream_t st);
+int b200_causal_softmax_fwd(void* s, int T_len, size_t rows, float scale, int is_bf16, cudaStream_t st);
+int b200_causal_softmax_bwd(const void* p, void* dp, int T_len, size_t rows, float scale, int is_bf16, cudaStream_t st);
+int b200_embedding_fwd(const long long* idx, const void* wte, const void* wpe, void* out, size_t rows, int T_len,
+                       int D, int is_bf16, cudaStream_t st);
+int b200_embedding_bwd(const long long* idx, const void* dout, float* dwte_acc, float* dwpe_acc, size_t rows,
+                       int T_len, int D, int is_bf16, cudaStream_t st);
+int b200_scale_inplace(void* x, size_t n, const float* scale_dev, int is_bf16, cudaStream_t st);
+int b200_xent_rows(const void* logits, const long long* target, void* dlogits, float* row_loss, float* loss,
+                   int B, int V, int ld, int is_bf16, cudaStream_t st);
 
 /* ---- peer-to-peer collectives over NVLink-mapped symmetric arenas (SURVEY K2-K6, W2-W7;
  * ProcessGroupNCCL on the reference path, REF:21).  `ctx` points to a HOST copy of the CommCtx

@@ -1,0 +1,76 @@
+"""GPT-2 module: CPU plumbing (always) and native-kernel numerics vs float64 (GPU)."""
+import pytest
+import torch
+
+import distributeddataparallel_b200 as d
+from distributeddataparallel_b200.models.gpt2 import build_gpt2
+
+
+def test_gpt2_medium_parameter_count():
+    import torch.nn as nn
+
+    with torch.device("meta"):
+        m = build_gpt2("gpt2-medium")
+    n = sum(p.numel() for p in m.parameters())
+    assert abs(n - 354.8e6) / 354.8e6 < 0.01, n
+
+
+def test_gpt2_tiny_trains_on_cpu():
+    torch.manual_seed(0)
+    m = build_gpt2("gpt2-tiny", seq_len=32)
+    opt = d.Adam(m.parameters(), lr=3e-3)
+    idx = torch.randint(0, 512, (4, 32))
+    tgt = torch.roll(idx, -1, dims=1)
+    first = None
+    for _ in range(20):
+        opt.zero_grad()
+        loss = m(idx, tgt)
+        loss.backward()
+        opt.step()
+        first = first if first is not None else float(loss)
+    assert float(loss) < first - 0.5
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-12))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 6e-2)])
+def test_gpt2_native_matches_fp64(dtype, tol):
+    torch.manual_seed(0)
+    ref = build_gpt2("gpt2-tiny", seq_len=64).double()
+    ref.wte.weight.data.mul_(5.0)                  # non-trivial logits
+    nat = build_gpt2("gpt2-tiny", seq_len=64)
+    nat.load_state_dict(ref.state_dict())
+    nat = nat.to("cuda", dtype)
+    idx = torch.randint(0, 512, (4, 64))
+    tgt = torch.randint(0, 512, (4, 64))
+    d.ops.set_native(False)
+    lr = ref(idx, tgt)
+    lr.backward()
+    d.ops.set_native(True)
+    ln = nat(idx.cuda(), tgt.cuda())
+    ln.backward()
+    torch.cuda.synchronize()
+    assert abs(float(ln) - float(lr)) < tol * max(1.0, abs(float(lr))), (float(ln), float(lr))
+    errs = {n: _rel(p.grad.cpu(), q.grad) for (n, p), (_, q) in zip(nat.named_parameters(), ref.named_parameters())}
+    worst = max(errs, key=errs.get)
+    assert errs[worst] < 8 * tol, (worst, errs[worst])
+    from distributeddataparallel_b200.ops import native
+
+    assert native.tc_error_word() == 0
+
+
+@pytest.mark.gpu
+def test_gpt2_ddp_graph_step_bf16():
+    torch.manual_seed(0)
+    model = build_gpt2("gpt2-tiny", seq_len=64).to("cuda", torch.bfloat16)
+    ddp = d.DDP(model, device_ids=[0])
+    opt = d.SGD(ddp.parameters(), lr=0.05)
+    step = d.TrainStep(ddp, None, opt, cuda_graph=True)
+    idx = torch.randint(0, 512, (4, 64), device="cuda")
+    tgt = torch.roll(idx, -1, dims=1)
+    losses = [float(step(idx, tgt)) for _ in range(12)]
+    assert step.captured and step.replays >= 8
+    assert losses[-1] < losses[0] - 0.2, losses
