@@ -34,6 +34,7 @@
 // Small-M convolutions (deep layers of a 32x32-input ResNet: 32..512 output pixels) run
 // "swapped": D^T = W * im2col(X)^T, so the 128-row MMA dimension is filled by output channels
 // and the few pixels become N; the epilogue stores transposed.
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdio.h>
 
@@ -101,6 +102,7 @@ struct Args {
   // batched GEMM (attention): blockIdx.z = batch index z, element offsets (z / inner) * s0 + (z % inner) * s1
   int batch, inner;
   long long a_s0, a_s1, b_s0, b_s1, o_s0, o_s1;
+  int tma_a, tma_b;            // operand is fetched by TMA (dense operands of non-batched calls)
 };
 
 __device__ __forceinline__ void store_out(const Args& a, float* out, size_t idx, float v) {
@@ -164,6 +166,17 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// 2-D tiled TMA load: box at (c0 = inner coordinate, c1 = outer coordinate) -> shared memory,
+// completion is counted in bytes on `bar`.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+
 template <bool BF16>
 __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
   if (BF16) {
@@ -331,7 +344,8 @@ struct TileLoader {
 };
 
 template <int AK, int BK_, int BN, bool BF16>
-__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
+__global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __grid_constant__ CUtensorMap map_a,
+                                                          const __grid_constant__ CUtensorMap map_b) {
   constexpr int ES = BF16 ? 2 : 4;
   constexpr int T = 16 / ES;
   constexpr int KELEMS = ROW_BYTES / ES;            // per stage
@@ -359,7 +373,8 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
 
   if (t == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], PRODUCERS);
+      // arrivals per stage: the 256 gather threads (if any operand is gathered) + the TMA issuer
+      mbar_init(&full_bar[s], ((a.tma_a && a.tma_b) ? 0 : PRODUCERS) + ((a.tma_a || a.tma_b) ? 1 : 0));
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(&accum_bar, 1);
@@ -375,29 +390,52 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
     // ================= producers =================
     TileLoader<AK, ES, BM> la;
     TileLoader<BK_, ES, BN> lb;
-    la.init(a_base, a.lda, a.g, m0, a.M, t);
-    lb.init(b_base, a.ldb, a.g, n0, a.N, t);
-    int issued = 0;
-    for (int kb = 0; kb < num_kb; ++kb) {
-      const int s = kb % STAGES;
-      if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1, a.error);
-      const int k0 = k_begin + kb * KELEMS;
-      la.load(smem_a + s * A_STAGE, a.g, k0, k_end);
-      lb.load(smem_b + s * B_STAGE, a.g, k0, k_end);
-      cp_async_commit();
-      ++issued;
-      if (issued >= STAGES - 1) {
-        // the oldest in-flight stage has landed: make it visible to the tensor core and publish it
-        cp_async_wait<STAGES - 2>();
+    const bool gather_a = !a.tma_a, gather_b = !a.tma_b;
+    if (gather_a) la.init(a_base, a.lda, a.g, m0, a.M, t);
+    if (gather_b) lb.init(b_base, a.ldb, a.g, n0, a.N, t);
+    const bool any_gather = gather_a || gather_b;
+    // TMA boxes: K-major operand = one box [ROWS x 128 B]; bf16 MN-major operand = ROWS/64 boxes of
+    // [64 k rows x 128 B of mn], 8 KB each.  Both land in the SWIZZLE_128B layout the MMA expects.
+    const uint32_t tx_bytes = (a.tma_a ? (uint32_t)A_STAGE : 0u) + (a.tma_b ? (uint32_t)B_STAGE : 0u);
+    if (any_gather || t == 0) {
+      int issued = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        if (kb >= STAGES) mbar_wait(&empty_bar[s], ((kb / STAGES) - 1) & 1, a.error);
+        const int k0 = k_begin + kb * KELEMS;
+        if (t == 0 && tx_bytes) {
+          mbar_expect_tx(&full_bar[s], tx_bytes);
+          if (a.tma_a) {
+            if (!is_mn(AK)) tma_load_2d(smem_a + s * A_STAGE, &map_a, k0, m0, &full_bar[s]);
+            else
+              for (int bx = 0; bx < BM / 64; ++bx) tma_load_2d(smem_a + s * A_STAGE + bx * 8192, &map_a, m0 + bx * 64, k0, &full_bar[s]);
+          }
+          if (a.tma_b) {
+            if (!is_mn(BK_)) tma_load_2d(smem_b + s * B_STAGE, &map_b, k0, n0, &full_bar[s]);
+            else
+              for (int bx = 0; bx < BN / 64; ++bx) tma_load_2d(smem_b + s * B_STAGE + bx * 8192, &map_b, n0 + bx * 64, k0, &full_bar[s]);
+          }
+        }
+        if (!any_gather) continue;
+        if (gather_a) la.load(smem_a + s * A_STAGE, a.g, k0, k_end);
+        if (gather_b) lb.load(smem_b + s * B_STAGE, a.g, k0, k_end);
+        cp_async_commit();
+        ++issued;
+        if (issued >= STAGES - 1) {
+          // the oldest in-flight stage has landed: make it visible to the tensor core and publish it
+          cp_async_wait<STAGES - 2>();
+          fence_proxy_async();
+          mbar_arrive(&full_bar[(kb - (STAGES - 2)) % STAGES]);
+        }
+      }
+      if (any_gather) {
+        // drain: publish the last min(num_kb, STAGES-2) stages
+        cp_async_wait<0>();
         fence_proxy_async();
-        mbar_arrive(&full_bar[(kb - (STAGES - 2)) % STAGES]);
+        const int first_unpublished = max(0, num_kb - (STAGES - 2));
+        for (int kb = first_unpublished; kb < num_kb; ++kb) mbar_arrive(&full_bar[kb % STAGES]);
       }
     }
-    // drain: publish the last min(num_kb, STAGES-2) stages
-    cp_async_wait<0>();
-    fence_proxy_async();
-    const int first_unpublished = max(0, num_kb - (STAGES - 2));
-    for (int kb = first_unpublished; kb < num_kb; ++kb) mbar_arrive(&full_bar[kb % STAGES]);
   } else if ((t & 31) == 0) {
     // ================= MMA issuer (one thread) =================
     constexpr uint32_t idesc = make_idesc(BF16, is_mn(AK), is_mn(BK_), BN);
@@ -420,8 +458,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
       tc_fence_after();
 #pragma unroll
       for (int j = 0; j < KELEMS / UMMA_K; ++j) {
-        const uint64_t da = make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
-        const uint64_t db = make_desc(smem_b + s * B_STAGE + j * B_STEP, B_LBO, B_SBO, B_TYPE);
+        // a TMA-fetched bf16 MN-major operand sits in the SWIZZLE_128B MN-major layout instead:
+        // 64-mn atoms 8 KB apart (LBO), 8-k-row atoms 1 KB apart (SBO), 2 k-atoms per MMA
+        const bool a_mn_tma = is_mn(AK) && a.tma_a, b_mn_tma = is_mn(BK_) && a.tma_b;
+        const uint64_t da = a_mn_tma ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
+                                     : make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
+        const uint64_t db = b_mn_tma ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
+                                     : make_desc(smem_b + s * B_STAGE + j * B_STEP, B_LBO, B_SBO, B_TYPE);
         umma<BF16>(tmem_d, da, db, idesc, (kb | j) ? 1u : 0u);
       }
       umma_commit(&empty_bar[s]);          // frees the stage when these MMAs have read it
@@ -621,16 +664,61 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a) {
 }
 
 // ---- host side ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+// 2-D row-major global matrix [outer x inner] with `pitch` elements per row; box [box_outer x box_inner];
+// 128-byte swizzle; out-of-range parts of a box are zero-filled.
+static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inner, long long outer, long long pitch,
+                     int box_inner, int box_outer) {
+  EncodeTiledFn fn = encode_tiled();
+  if (!fn) return false;
+  const int es = bf16 ? 2 : 4;
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * es};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
+            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static bool g_use_tma = true;
+
 template <int AK, int BK_, int BN, bool BF16>
-static int launch(const Args& a, dim3 grid, cudaStream_t st) {
+static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
   constexpr int smem = STAGES * (BM + BN) * ROW_BYTES + 1024;
+  constexpr int KELEMS = ROW_BYTES / (BF16 ? 2 : 4);
+  Args a = a_in;
+  CUtensorMap map_a{}, map_b{};
+  a.tma_a = a.tma_b = 0;
+  if (g_use_tma && a.batch <= 1) {
+    // dense K-major: matrix [rows x K]; dense bf16 MN-major: matrix [K x mn], boxes of 64 mn x KELEMS k
+    if (AK == DENSE_K) a.tma_a = make_map(&map_a, a.a, BF16, a.Kd, a.M, a.lda, KELEMS, BM);
+    else if (AK == DENSE_MN && BF16) a.tma_a = make_map(&map_a, a.a, true, a.M, a.Kd, a.lda, 64, KELEMS);
+    if (BK_ == DENSE_K) a.tma_b = make_map(&map_b, a.b, BF16, a.Kd, a.N, a.ldb, KELEMS, BN);
+    else if (BK_ == DENSE_MN && BF16 && BN >= 64) a.tma_b = make_map(&map_b, a.b, true, a.N, a.Kd, a.ldb, 64, KELEMS);
+  }
   static bool configured = false;     // per template instantiation
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_kernel<AK, BK_, BN, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
   }
-  gemm_kernel<AK, BK_, BN, BF16><<<grid, THREADS, smem, st>>>(a);
+  gemm_kernel<AK, BK_, BN, BF16><<<grid, THREADS, smem, st>>>(a, map_a, map_b);
   return static_cast<int>(cudaPeekAtLastError());
 }
 
@@ -670,6 +758,9 @@ using namespace b200;
 using namespace b200::tc;
 
 static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
+B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 
 // Dense (optionally batched) GEMM; inputs fp32 (TF32 math) or bf16, output fp32 or bf16:
 //   mode 0 (NT): out[M,N] = A[M,K]  * B[N,K]^T      (Linear forward:  x, W)

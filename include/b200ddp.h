@@ -121,6 +121,7 @@ int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, in
 int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, int mode,
                     int flags, const long long* desc, float* workspace, size_t workspace_bytes,
                     unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
+void b200_gemm_tc_use_tma(int enabled);   /* dense operands via TMA (default) or cp.async gathers */
 int b200_conv2d_fprop_tc(const float* x, const float* w, float* y, float* stats, int Nb, int H, int W, int C,
                          int K, int R, int S, int stride, int pad, float* workspace, size_t workspace_bytes,
                          unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
