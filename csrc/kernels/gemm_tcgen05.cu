@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   constexpr int KELEMS = ROW_BYTES / ES;            // per stage
   constexpr int UMMA_K = 32 / ES;                   // 8 (tf32) / 16 (bf16)
   constexpr int A_STAGE = BM * ROW_BYTES, B_STAGE = BN * ROW_BYTES;
-  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;          // 32 / 64 / 128 / 256: powers of two
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar;
   __shared__ uint32_t tmem_base_s;
@@ -484,12 +484,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
     const int tiles = gridDim.x * gridDim.y;
     const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
     bool writer = true;
-    float acc[NCH][16];
-#pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-      if (COLS_PER_WARP >= 16 || col_half == 0)
-        tmem_ld16(tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(col_base + c * 16), acc[c]);
-    }
+    // the accumulator is streamed out of TMEM 16 columns at a time (keeps the epilogue at 16 live
+    // accumulator registers even for 256-column tiles)
+    const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)col_base;
     if (a.splits > 1) {
       // ---- split-K: park the partial tile, then ALL splits of this tile reduce it together ----
       // Every split CTA sums one slice of rows over all parked partials and writes that slice of
@@ -497,10 +494,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
       // there are (a lone "last CTA reduces everything" step would serialise splits x 64 KB).
       // Needs the splits of a tile co-resident: the host keeps tiles*splits <= 128 CTAs (1 per SM).
       float* mine = a.workspace + ((size_t)split_z * tiles + tile_id) * (BM * BN);
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        float acc[16];
+        tmem_ld16(tmem_row + c * 16, acc);
 #pragma unroll
-      for (int c = 0; c < NCH; ++c)
-#pragma unroll
-        for (int j = 0; j < 16; ++j) mine[(size_t)(col_base + c * 16 + j) * BM + row] = acc[c][j];
+        for (int j = 0; j < 16; ++j) mine[(size_t)(col_base + c * 16 + j) * BM + row] = acc[j];
+      }
       __threadfence();
       asm volatile("bar.sync 1, 256;" ::: "memory");           // producer/epilogue warps only
       unsigned* arrive = a.counters + 2 * tile_id;
@@ -601,18 +601,21 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         // stores of one accumulator column are already coalesced (out[col * ldo + row])
         float rsum = 0.f, rsq = 0.f;
         const float bias = (a.bias != nullptr && row_ok) ? load_bias(a, grow) : 0.f;
-#pragma unroll
-        for (int c = 0; c < NCH; ++c)
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float acc[16];
+          tmem_ld16(tmem_row + c * 16, acc);
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int gcol = n0 + col_base + c * 16 + j;
             if (row_ok && gcol < a.N) {
-              const float v = acc[c][j] + bias;
+              const float v = acc[j] + bias;
               store_out(a, out_base, (size_t)gcol * a.ldo + grow, v);
               rsum += v;
               rsq += v * v;
             }
           }
+        }
         if (a.stats != nullptr && row_ok) {
           atomicAdd(a.stats + grow, rsum);
           atomicAdd(a.stats + a.M + grow, rsq);
@@ -622,16 +625,19 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         // are 128-byte row segments and the BatchNorm column sums come from conflict-free smem reads
         float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
         constexpr int LDS = BN + 1;
-#pragma unroll
-        for (int c = 0; c < NCH; ++c)
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float acc[16];
+          tmem_ld16(tmem_row + c * 16, acc);
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int col = col_base + c * 16 + j;
             const int gcol = n0 + col;
-            float v = acc[c][j];
+            float v = acc[j];
             if (a.bias != nullptr && gcol < a.N) v += load_bias(a, gcol);
             stage[row * LDS + col] = v;
           }
+        }
         asm volatile("bar.sync 1, 256;" ::: "memory");
         const int lane = t & 31;
 #pragma unroll 4
@@ -726,7 +732,10 @@ template <int AK, int BK_, bool BF16>
 static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int force_bn, cudaStream_t st) {
   constexpr int ES = BF16 ? 2 : 4;
   constexpr int KELEMS = ROW_BYTES / ES;
+  // 256-wide tiles halve the A traffic per flop (L2 bandwidth is what bounds 128x128 tiles); use them
+  // when the problem is big enough to still fill the chip
   int bn = force_bn ? force_bn : (a.N <= 32 ? 32 : (a.N <= 64 ? 64 : 128));
+  if (!force_bn && a.batch <= 1 && a.N >= 256 && (long long)ceil_div(a.M, BM) * ceil_div(a.N, 256) >= 2 * kNumSMs) bn = 256;
   const int tm = ceil_div(a.M, BM), tn = ceil_div(a.N, bn);
   const int tiles = tm * tn;
   const int k_blocks = ceil_div(a.Kd, KELEMS);
@@ -748,6 +757,7 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   dim3 grid(tm, tn, a.batch > 1 ? a.batch : a.splits);
   if (bn == 32) return launch<AK, BK_, 32, BF16>(a, grid, st);
   if (bn == 64) return launch<AK, BK_, 64, BF16>(a, grid, st);
+  if (bn == 256) return launch<AK, BK_, 256, BF16>(a, grid, st);
   return launch<AK, BK_, 128, BF16>(a, grid, st);
 }
 
@@ -828,11 +838,14 @@ B200_API int b200_conv2d_fprop_tc(const float* x, const float* w, float* y, floa
   const int pixels = Nb * a.g.P * a.g.Q;
   a.Kd = R * S * C; a.stats = stats; a.workspace = workspace; a.counters = counters; a.error = error; a.out = y;
   a.ldo = K;
+  const bool pointwise = R == 1 && S == 1 && stride == 1 && pad == 0;   // a plain GEMM: X is [pixels, C] dense
   if (pixels >= 1024 || K < 128) {       // pixels fill the 128-row MMA dimension
-    a.a = x; a.b = w; a.ldb = a.Kd; a.M = pixels; a.N = K;
+    a.a = x; a.b = w; a.lda = C; a.ldb = a.Kd; a.M = pixels; a.N = K;
+    if (pointwise) return dispatch_bn<DENSE_K, DENSE_K, false>(a, workspace_bytes, max_counters, 0, stream);
     return dispatch_bn<IM2COL_K, DENSE_K, false>(a, workspace_bytes, max_counters, 0, stream);
   }
-  a.a = w; a.b = x; a.lda = a.Kd; a.M = K; a.N = pixels; a.transpose_out = 1;   // swapped: channels are rows
+  a.a = w; a.b = x; a.lda = a.Kd; a.ldb = C; a.M = K; a.N = pixels; a.transpose_out = 1;   // swapped: channels are rows
+  if (pointwise) return dispatch_bn<DENSE_K, DENSE_K, false>(a, workspace_bytes, max_counters, 0, stream);
   return dispatch_bn<DENSE_K, IM2COL_K, false>(a, workspace_bytes, max_counters, 0, stream);
 }
 
@@ -844,11 +857,14 @@ B200_API int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, in
   a.g = make_geom(Nb, H, W, C, K, R, S, stride, pad);
   const int pixels = Nb * H * W;
   a.Kd = R * S * K; a.workspace = workspace; a.counters = counters; a.error = error; a.out = dx; a.ldo = C;
+  const bool pointwise = R == 1 && S == 1 && stride == 1 && pad == 0;   // dX = dY[pixels,K] * W[K,C]
   if (pixels >= 1024 || C < 128) {
-    a.a = dy; a.b = w; a.M = pixels; a.N = C;
+    a.a = dy; a.b = w; a.lda = K; a.ldb = C; a.M = pixels; a.N = C;
+    if (pointwise) return dispatch_bn<DENSE_K, DENSE_MN, false>(a, workspace_bytes, max_counters, 0, stream);
     return dispatch_bn<IM2COL_T_K, WEIGHT_T_MN, false>(a, workspace_bytes, max_counters, 0, stream);
   }
-  a.a = w; a.b = dy; a.M = C; a.N = pixels; a.transpose_out = 1;
+  a.a = w; a.b = dy; a.lda = C; a.ldb = K; a.M = C; a.N = pixels; a.transpose_out = 1;
+  if (pointwise) return dispatch_bn<DENSE_MN, DENSE_K, false>(a, workspace_bytes, max_counters, 0, stream);
   return dispatch_bn<WEIGHT_T_MN, IM2COL_T_K, false>(a, workspace_bytes, max_counters, 0, stream);
 }
 
@@ -861,5 +877,9 @@ B200_API int b200_conv2d_wgrad_tc(const float* dy, const float* x, float* dw, in
   a.g = make_geom(Nb, H, W, C, K, R, S, stride, pad);
   a.a = dy; a.lda = K; a.b = x; a.M = K; a.N = R * S * C; a.Kd = Nb * a.g.P * a.g.Q;
   a.workspace = workspace; a.counters = counters; a.error = error; a.out = dw; a.ldo = a.N; a.accumulate = accumulate;
+  if (R == 1 && S == 1 && stride == 1 && pad == 0) {      // dW[K,C] = dY[pixels,K]^T * X[pixels,C]
+    a.ldb = C;
+    return dispatch_bn<DENSE_MN, DENSE_MN, false>(a, workspace_bytes, max_counters, 0, stream);
+  }
   return dispatch_bn<DENSE_MN, IM2COL_MN, false>(a, workspace_bytes, max_counters, 0, stream);
 }

@@ -25,7 +25,8 @@ def _cl(t):
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-3), (torch.bfloat16, 1e-2)])
-@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (256, 128, 512), (32, 16, 512), (1000, 200, 328), (4096, 1024, 1024)])
+@pytest.mark.parametrize("m,n,k", [(128, 64, 64), (256, 128, 512), (32, 16, 512), (1000, 200, 328), (4096, 1024, 1024),
+                                   (16384, 2048, 512)])      # the last one takes the 128x256 tile path
 def test_dense_gemm_three_layouts(nat, dtype, tol, m, n, k):
     torch.manual_seed(0)
     a = torch.randn(m, k, device="cuda").to(dtype)
@@ -57,7 +58,9 @@ CONV_SHAPES = [
     (32, 64, 8, 64, 3, 1, 1), (32, 64, 8, 128, 3, 2, 1), (32, 128, 4, 128, 3, 1, 1), (32, 64, 8, 128, 1, 2, 0),
     (32, 128, 4, 256, 3, 2, 1), (32, 256, 2, 256, 3, 1, 1), (32, 256, 2, 512, 3, 2, 1), (32, 512, 1, 512, 3, 1, 1),
     (32, 256, 2, 512, 1, 2, 0), (10, 64, 8, 64, 3, 1, 1), (10, 512, 1, 512, 3, 1, 1), (8, 64, 56, 64, 3, 1, 1),
-    (8, 256, 14, 1024, 1, 1, 0),
+    (8, 256, 14, 1024, 1, 1, 0),       # pointwise, stride 1: dispatched as a dense (TMA) GEMM
+    (32, 512, 1, 2048, 1, 1, 0),       # pointwise, tiny pixel count: swapped dense GEMM
+    (16, 64, 56, 256, 1, 1, 0),
 ]
 
 
