@@ -83,6 +83,22 @@ struct Geom {
   FastDiv fQ, fP, fC, fS, fW, fH, fK, fStride;
 };
 
+// GEMM whose epilogue IS the cross-GPU gradient reduction (north-star fusion):
+// every rank computes its partial of each output tile; a tile's owner (tile_id % world) receives
+// the peers' partials in its staging area over NVLink, sums them in rank order, scales by 1/world
+// and pushes the finished tile into EVERY rank's copy of the output (the gradient-bucket slot).
+// Tiles of different owners are in flight at once, so the transfer of tile i overlaps the MMA
+// of tile i+1 on every GPU.  All pointers are peer mappings of symmetric-arena objects.
+struct PeerReduce {
+  float* out[8];          // each rank's output matrix (same offset in every arena)
+  float* stage[8];        // each rank's staging area  [src rank][tile][BN][BM] fp32
+  uint32_t* flags[8];     // each rank's flags         [tile][8] "partial from src arrived", then [tile] "tile final"
+  uint32_t* epoch;        // local launch counter (bumped by peer_reduce_wait_kernel)
+  int rank, world;
+  float scale;
+  int pad;
+};
+
 struct Args {
   const void* a;
   const void* b;
@@ -103,6 +119,7 @@ struct Args {
   int batch, inner;
   long long a_s0, a_s1, b_s0, b_s1, o_s0, o_s1;
   int tma_a, tma_b;            // operand is fetched by TMA (dense operands of non-batched calls)
+  PeerReduce peer;             // world > 1: fused all-reduce epilogue (needs splits == 1, row-major out)
 };
 
 __device__ __forceinline__ void store_out(const Args& a, float* out, size_t idx, float v) {
@@ -593,6 +610,79 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
       }
       writer = false;
     }
+    if (a.peer.world > 1) {
+      // ---- fused cross-GPU reduction of this tile ------------------------------------------------
+      const PeerReduce& pr = a.peer;
+      const int owner = tile_id % pr.world;
+      const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(pr.epoch) + 1u;
+      float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
+      constexpr int LDS = BN + 1;
+      const int lane = t & 31;
+      if (pr.rank != owner) {
+        // partial tile -> owner's staging area ([col][row]: lanes write consecutive rows, 128 B per warp store)
+        float* dst = pr.stage[owner] + ((size_t)pr.rank * tiles + tile_id) * (BM * BN);
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float acc[16];
+          tmem_ld16(tmem_row + c * 16, acc);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dst[(size_t)(col_base + c * 16 + j) * BM + row] = acc[j];
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (t == 0) st_release_sys(pr.flags[owner] + (size_t)tile_id * 8 + pr.rank, epoch);
+      } else {
+        // own partial -> shared memory, then add the peers' partials as they arrive
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          float acc[16];
+          tmem_ld16(tmem_row + c * 16, acc);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) stage[row * LDS + col_base + c * 16 + j] = acc[j];
+        }
+        if (t < pr.world && t != pr.rank) {
+          const uint32_t* f = pr.flags[pr.rank] + (size_t)tile_id * 8 + t;
+          unsigned spins = 0;
+          while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+            if (++spins > kWaitLimit) {
+              if (a.error) atomicExch(a.error, 0xBAD0FEEDu);
+              break;
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float* mine = pr.stage[pr.rank] + (size_t)tile_id * (BM * BN);
+        const size_t src_stride = (size_t)tiles * (BM * BN);
+        for (int idx = t; idx < BM * BN; idx += PRODUCERS) {
+          const int r = idx % BM, c = idx / BM;                 // lanes walk rows: coalesced staged reads
+          float v = 0.f;
+          for (int p = 0; p < pr.world; ++p)                    // fixed rank order
+            v += (p == pr.rank) ? stage[r * LDS + c] : __ldcg(mine + p * src_stride + (size_t)c * BM + r);
+          stage[r * LDS + c] = v * pr.scale;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        // finished tile -> every rank's output, 128-byte row segments
+        for (int rr = warp; rr < BM; rr += 8) {
+          const int gr = m0 + rr;
+          if (gr >= a.M) break;
+          for (int col = lane; col < BN; col += 32) {
+            const int gc = n0 + col;
+            if (gc < a.N) {
+              const float v = stage[rr * LDS + col];
+              const size_t o = (size_t)gr * a.ldo + gc;
+#pragma unroll
+              for (int p = 0; p < 8; ++p)
+                if (p < pr.world) {
+                  if (a.out_bf16) reinterpret_cast<__nv_bfloat16*>(pr.out[p])[o] = __float2bfloat16_rn(v);
+                  else pr.out[p][o] = v;
+                }
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (t < pr.world) st_release_sys(pr.flags[t] + (size_t)tiles * 8 + tile_id, epoch);   // "tile final" on every rank
+      }
+      writer = false;
+    }
     if (writer) {
       const int grow = m0 + row;
       const bool row_ok = grow < a.M;
@@ -669,6 +759,24 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   if (warp == 8) tmem_dealloc(tmem_d, TMEM_COLS);
 }
 
+// After a fused-reduction GEMM: wait until every tile of the output has been finalised in THIS rank's
+// copy (owners signal "tile final" on all ranks), then advance the launch counter.
+__global__ void __launch_bounds__(256) peer_reduce_wait_kernel(PeerReduce pr, int tiles, unsigned* error) {
+  const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(pr.epoch) + 1u;
+  for (int tile = threadIdx.x; tile < tiles; tile += blockDim.x) {
+    const uint32_t* f = pr.flags[pr.rank] + (size_t)tiles * 8 + tile;
+    unsigned spins = 0;
+    while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+      if (++spins > kWaitLimit) {
+        if (error) atomicExch(error, 0xBAD0D07Eu);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *pr.epoch = epoch;
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -742,7 +850,7 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
   int splits = 1;
   if (a.batch < 1) a.batch = 1;
   if (a.inner < 1) a.inner = 1;
-  if (a.batch == 1 && tiles < 64 && a.workspace && a.counters && 2 * tiles <= max_counters && k_blocks >= 4) {
+  if (a.peer.world <= 1 && a.batch == 1 && tiles < 64 && a.workspace && a.counters && 2 * tiles <= max_counters && k_blocks >= 4) {
     // One CTA keeps at most 3 stages (96 KB) of loads in flight, i.e. ~60-100 GB/s at DRAM/L2
     // latency: streaming the operands fast needs MANY CTAs, so K is split until ~128 CTAs run
     // (all co-resident, one per SM: the splits of a tile wait for each other in the epilogue).
@@ -883,3 +991,43 @@ B200_API int b200_conv2d_wgrad_tc(const float* dy, const float* x, float* dw, in
   }
   return dispatch_bn<DENSE_MN, IM2COL_MN, false>(a, workspace_bytes, max_counters, 0, stream);
 }
+
+// Fused "weight-gradient GEMM + all-reduce (average)" (SURVEY W12).  Same operand conventions as
+// b200_gemm_tc_ex; `peer` is a host copy of PeerReduce filled with this process's mappings of every
+// rank's output / staging / flag objects.  The output must be row-major (no split-K, no batching);
+// staging needs world * tiles * 128 * BN * 4 bytes per rank, flags tiles * 9 words, where
+// tiles = ceil(M/128) * ceil(N/BN) and BN is returned by b200_gemm_tc_peer_bn(N).  A trailing
+// one-block kernel waits for the tiles other owners push into this rank's copy.
+B200_API int b200_gemm_tc_peer_bn(int N) { return N <= 32 ? 32 : (N <= 64 ? 64 : 128); }
+
+B200_API int b200_gemm_tc_peer(const void* A, const void* B, const void* bias, int M, int N, int K, int mode, int flags,
+                               const long long* desc, const void* peer, unsigned* error, cudaStream_t stream) {
+  const bool bf16 = flags & 1;
+  const int vec = bf16 ? 8 : 4;
+  if (!ptr16(A) || !ptr16(B) || M <= 0 || N <= 0 || K <= 0) return static_cast<int>(cudaErrorInvalidValue);
+  Args a{};
+  a.peer = *static_cast<const PeerReduce*>(peer);
+  if (a.peer.world < 2 || a.peer.world > 8) return static_cast<int>(cudaErrorInvalidValue);
+  a.a = A; a.b = B; a.out = a.peer.out[a.peer.rank]; a.bias = static_cast<const float*>(bias);
+  a.M = M; a.N = N; a.Kd = K;
+  a.lda = desc[0]; a.ldb = desc[1]; a.ldo = desc[2];
+  a.batch = 1; a.inner = 1;
+  a.out_bf16 = (flags >> 1) & 1; a.bias_bf16 = (flags >> 2) & 1;
+  a.error = error;
+  if (a.lda % vec || a.ldb % vec) return static_cast<int>(cudaErrorInvalidValue);
+  const int bn = b200_gemm_tc_peer_bn(N);
+  int rc;
+#define B200_GEMM_MODE(AK, BKIND)                                                        \
+  rc = bf16 ? dispatch_bn<AK, BKIND, true>(a, 0, 0, bn, stream) : dispatch_bn<AK, BKIND, false>(a, 0, 0, bn, stream)
+  if (mode == 0) { B200_GEMM_MODE(DENSE_K, DENSE_K); }
+  else if (mode == 1) { B200_GEMM_MODE(DENSE_K, DENSE_MN); }
+  else if (mode == 2) { B200_GEMM_MODE(DENSE_MN, DENSE_MN); }
+  else return static_cast<int>(cudaErrorInvalidValue);
+#undef B200_GEMM_MODE
+  if (rc != 0) return rc;
+  const int tiles = ceil_div(M, BM) * ceil_div(N, bn);
+  peer_reduce_wait_kernel<<<1, 256, 0, stream>>>(a.peer, tiles, error);
+  return static_cast<int>(cudaPeekAtLastError());
+}
+
+B200_API int b200_peer_reduce_bytes(void) { return (int)sizeof(PeerReduce); }

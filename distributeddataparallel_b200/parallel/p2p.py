@@ -353,3 +353,67 @@ class EmulatedWorld:
 
     def error_word(self) -> int:
         return int(self.error[0].item()) & 0xFFFFFFFF
+
+
+class FusedGradReduce:
+    """Weight-gradient GEMM whose epilogue is the all-reduce.
+
+    ``dW = average_over_ranks(dY_r^T @ X_r)`` computed by ONE tcgen05 kernel per rank: partial
+    tiles are pushed over NVLink to their owner rank, the owner sums them in rank order and pushes
+    the finished tile into every rank's copy of ``out`` (which must live in the symmetric arena,
+    e.g. a gradient-bucket slot), so the transfer of one tile overlaps the MMA of the next.
+    """
+
+    BM = 128
+
+    def __init__(self, comm: "P2PComm") -> None:
+        self.comm = comm
+        self._stage = None          # (offset, bytes)
+        self._flags = None          # (offset, words)
+        self._epoch = None
+        lib = _lib()
+        assert lib.b200_peer_reduce_bytes() == 216, lib.b200_peer_reduce_bytes()
+
+    def _reserve(self, tiles: int, bn: int) -> None:
+        arena = self.comm.arena
+        world = self.comm.world_size
+        need = world * tiles * self.BM * bn * 4
+        if self._stage is None or self._stage[1] < need:
+            self._stage = (arena.alloc(need), need)
+        words = tiles * 9
+        if self._flags is None or self._flags[1] < words:
+            off = arena.alloc(words * 4)
+            arena.memory[off:off + words * 4].zero_()
+            self._flags = (off, words)
+        if self._epoch is None:
+            self._epoch = arena.alloc(256)
+            arena.memory[self._epoch:self._epoch + 256].zero_()
+
+    def wgrad(self, dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor) -> None:
+        """out[N_out, K_in] (arena resident, same offset on every rank) = mean_r(dy_r^T @ x_r)."""
+        arena = self.comm.arena
+        off = arena.offset_of(out)
+        if off is None or not out.is_contiguous():
+            raise RuntimeError("fused gradient reduction needs a contiguous output inside the symmetric arena")
+        m_tok, n_out = dy.shape
+        k_in = x.shape[1]
+        lib = _lib()
+        bn = lib.b200_gemm_tc_peer_bn(ctypes.c_int(k_in))
+        tiles = -(-n_out // self.BM) * -(-k_in // bn)
+        self._reserve(tiles, bn)
+        world, rank = self.comm.world_size, self.comm.rank
+        pb = arena.peer_base
+        pad = [0] * (8 - world)
+        raw = struct.pack("<8Q8Q8QQiifi",
+                          *[b + off for b in pb], *pad,
+                          *[b + self._stage[0] for b in pb], *pad,
+                          *[b + self._flags[0] for b in pb], *pad,
+                          arena.base + self._epoch, rank, world, 1.0 / world, 0)
+        peer = ctypes.create_string_buffer(raw, len(raw))
+        flags = int(dy.dtype == torch.bfloat16) | (int(out.dtype == torch.bfloat16) << 1)
+        desc = (ctypes.c_longlong * 11)(n_out, k_in, k_in, 1, 1, 0, 0, 0, 0, 0, 0)
+        err = native.scratch(dy.device).error
+        native._call("b200_gemm_tc_peer", ctypes.c_void_p(dy.data_ptr()), ctypes.c_void_p(x.data_ptr()),
+                     ctypes.c_void_p(0), ctypes.c_int(n_out), ctypes.c_int(k_in), ctypes.c_int(m_tok), ctypes.c_int(2),
+                     ctypes.c_int(flags), desc, peer, ctypes.c_void_p(err.data_ptr()),
+                     ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), kernels=2)

@@ -121,6 +121,13 @@ int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, in
 int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, int mode,
                     int flags, const long long* desc, float* workspace, size_t workspace_bytes,
                     unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
+/* weight-gradient GEMM fused with the all-reduce (average) of its output over NVLink peers: the
+ * epilogue pushes partial tiles to their owner rank and finished tiles into every rank's copy
+ * (SURVEY W12).  `peer` = host copy of the PeerReduce struct in csrc/kernels/gemm_tcgen05.cu. */
+int b200_gemm_tc_peer_bn(int N);
+int b200_peer_reduce_bytes(void);
+int b200_gemm_tc_peer(const void* A, const void* B, const void* bias, int M, int N, int K, int mode, int flags,
+                      const long long* desc, const void* peer, unsigned* error, cudaStream_t stream);
 void b200_gemm_tc_use_tma(int enabled);   /* dense operands via TMA (default) or cp.async gathers */
 int b200_conv2d_fprop_tc(const float* x, const float* w, float* y, float* stats, int Nb, int H, int W, int C,
                          int K, int R, int S, int stride, int pad, float* workspace, size_t workspace_bytes,

@@ -108,3 +108,60 @@ def ddp_worker(rank, ws, port, out_dir):
     torch.save(rec, os.path.join(out_dir, f"ddp{rank}.pt"))
     del step
     d.cleanup()
+
+
+def fused_wgrad_worker(rank, ws, port, out_dir):
+    """GEMM + all-reduce in one kernel vs GEMM followed by the all-reduce kernel."""
+    d = _init(rank, ws, port)
+    from distributeddataparallel_b200.ops import native
+    from distributeddataparallel_b200.parallel.p2p import FusedGradReduce, P2PComm
+
+    dev = torch.device("cuda", rank)
+    comm = P2PComm(None, dev)
+    comm.reserve(512 << 20)
+    fused = FusedGradReduce(comm)
+    rec = {"ok": True, "fails": [], "times": {}}
+    g = torch.Generator(device="cpu").manual_seed(100 + rank)
+    for dtype in (torch.bfloat16, torch.float32):
+        for (tok, n_out, k_in) in [(1024, 256, 128), (4096, 1024, 1024), (8192, 4096, 1024)]:
+            dy = torch.randn(tok, n_out, generator=g).to(dtype).to(dev)
+            x = torch.randn(tok, k_in, generator=g).to(dtype).to(dev)
+            out = comm.allocate(n_out * k_in, dtype, dev).view(n_out, k_in)
+            ref = (dy.double().t() @ x.double())
+            dist.all_reduce(ref)
+            ref /= ws
+            for rep in range(3):                         # repeated launches reuse staging / flags
+                out.zero_()
+                torch.cuda.synchronize(); dist.barrier()
+                fused.wgrad(dy, x, out)
+            torch.cuda.synchronize()
+            gathered = [torch.empty_like(out) for _ in range(ws)]
+            dist.all_gather(gathered, out)
+            same = all(torch.equal(gathered[0], t) for t in gathered)
+            err = float((out.double() - ref).norm() / ref.norm())
+            tol = 2e-2 if dtype == torch.bfloat16 else 3e-3
+            if not (same and err < tol):
+                rec["ok"] = False
+                rec["fails"].append((str(dtype), tok, n_out, k_in, same, err))
+            # timing: fused vs unfused (GEMM into the arena slot, then the two-shot all-reduce)
+            def unfused():
+                native.gemm_tc(dy.t().contiguous() if False else dy, x, 2, out=None) if False else None
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            from distributeddataparallel_b200.ops import native_tf
+            tmp = comm.allocate(n_out * k_in, torch.float32, dev).view(n_out, k_in) if dtype == torch.float32 else \
+                comm.allocate(n_out * k_in, dtype, dev).view(n_out, k_in)
+            torch.cuda.synchronize(); dist.barrier()
+            e0.record()
+            for _ in range(5):
+                fused.wgrad(dy, x, out)
+            e1.record()
+            for _ in range(5):
+                native_tf.gemm_ex(dy, x, tmp, 2, n_out, k_in, tok, n_out, k_in, k_in)
+                comm.all_reduce_avg_(tmp.view(-1))
+            e2.record()
+            torch.cuda.synchronize()
+            rec["times"][(str(dtype), tok, n_out, k_in)] = (e0.elapsed_time(e1) / 5, e1.elapsed_time(e2) / 5)
+    comm.check()
+    rec["tc_error"] = native.tc_error_word(dev)
+    torch.save(rec, os.path.join(out_dir, f"fused{rank}.pt"))
+    d.cleanup()

@@ -39,3 +39,12 @@ def test_ddp_p2p_end_to_end(tmp_path):
         assert rec["grad_err_vs_nccl"] < 0.1, rec["grad_err_vs_nccl"]   # two separate forward passes: BN float-atomic noise, amplified
         assert rec["graph_replays"] >= 3 and rec["error_word"] == 0
         assert rec["rebuilt"] == [9_461_800, 26_494_976, 8_769_792]
+
+
+def test_fused_wgrad_allreduce(tmp_path):
+    n = min(_n(), 4)
+    mp.spawn(W.fused_wgrad_worker, args=(n, _port(), str(tmp_path)), nprocs=n, join=True)
+    for r in range(n):
+        rec = torch.load(tmp_path / f"fused{r}.pt")
+        assert rec["ok"] and rec["tc_error"] == 0, rec
+    print("fused vs unfused ms:", torch.load(tmp_path / "fused0.pt")["times"])
