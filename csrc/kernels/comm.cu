@@ -52,6 +52,7 @@ struct CommCtx {
   uint32_t* epochs;                 // local: [rank (emulation only)][channel][block]
   uint32_t* error;                  // local error word
   int rank, world, channel, emulate;
+  unsigned char* mc;                // NVLS: multicast mapping of the arenas (0 if the box has none)
 };
 
 __device__ __forceinline__ int ctx_rank(const CommCtx& c) { return c.emulate ? (int)blockIdx.y : c.rank; }
@@ -171,6 +172,65 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
   block_barrier(c, rank);
 }
 
+// ---- NVLS (in-switch reduction through the NVLink multicast mapping) ---------------------------------
+// multimem.ld_reduce on the multicast address returns the SUM over every rank's copy, computed
+// inside NVSwitch; multimem.st writes all copies at once.  Rank r handles slice r: ingress per GPU
+// drops from 2(N-1)/N*S to ~S/N*... (one reduced stream in, one broadcast stream out) and only a few
+// SMs are needed.  Requires the arena to be a multicast-bound allocation (symm_mem provider).
+template <typename T> struct Multimem;
+template <> struct Multimem<float> {
+  __device__ static uint4 ld_reduce(const void* p) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+  }
+  __device__ static void st(void* p, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+};
+template <> struct Multimem<__nv_bfloat16> {
+  __device__ static uint4 ld_reduce(const void* p) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+  }
+  __device__ static void st(void* p, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+                 ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommCtx c, size_t offset, size_t nvec, float scale) {
+  const int rank = ctx_rank(c), N = c.world;
+  block_barrier(c, rank);
+  const size_t per = (nvec + N - 1) / N;
+  const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
+  constexpr int U = 4;
+  const size_t trip = (size_t)gridDim.x * blockDim.x * U;
+  for (size_t base = begin + (size_t)blockIdx.x * blockDim.x * U + threadIdx.x; base < end; base += trip) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i < end) v[u] = Multimem<T>::ld_reduce(c.mc + offset + i * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + (size_t)u * blockDim.x;
+      if (i >= end) continue;
+      float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      Vec<T>::acc(a, v[u]);
+      Multimem<T>::st(c.mc + offset + i * 16, Vec<T>::pack(a, scale));
+    }
+  }
+  __threadfence_system();
+  block_barrier(c, rank);
+}
+
 // ---- one-shot ------------------------------------------------------------------------------------
 constexpr int kOneShotVecPerThread = 4;
 template <typename T>
@@ -270,7 +330,7 @@ B200_API size_t b200_allreduce_oneshot_max_bytes(void) {
   return (size_t)kMaxCommBlocks * 512 * kOneShotVecPerThread * 16;
 }
 
-// dtype: 0 = fp32, 1 = bf16.  algo: 1 = one-shot, 2 = two-shot.  `nbytes` must be a multiple of 16.
+// dtype: 0 = fp32, 1 = bf16.  algo: 1 = one-shot, 2 = two-shot, 3 = NVLS multimem.  `nbytes` % 16 == 0.
 B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, int algo,
                             int max_blocks, cudaStream_t stream) {
   const CommCtx& c = *static_cast<const CommCtx*>(ctx);
@@ -285,6 +345,12 @@ B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int d
     if (dtype == 0)
       return launch_comm(allreduce_oneshot_kernel<float>, c, (int)blocks, 512, stream, offset, nvec, scale);
     return launch_comm(allreduce_oneshot_kernel<__nv_bfloat16>, c, (int)blocks, 512, stream, offset, nvec, scale);
+  }
+  if (algo == 3) {          // NVLS
+    if (c.mc == nullptr || c.emulate) return static_cast<int>(cudaErrorNotSupported);
+    const int nb = pick_blocks((nvec + c.world - 1) / c.world, min(max_blocks, 24));
+    if (dtype == 0) return launch_comm(allreduce_nvls_kernel<float>, c, nb, 512, stream, offset, nvec, scale);
+    return launch_comm(allreduce_nvls_kernel<__nv_bfloat16>, c, nb, 512, stream, offset, nvec, scale);
   }
   const int blocks = pick_blocks((nvec + c.world - 1) / c.world, max_blocks);
 #define B200_TWOSHOT(T)                                                                                          \

@@ -43,10 +43,10 @@ def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
 
 
 def _pack_ctx(bufs: Sequence[int], flags: Sequence[int], epochs: int, error: int, rank: int, world: int,
-              channel: int, emulate: int) -> ctypes.Array:
+              channel: int, emulate: int, multicast: int = 0) -> ctypes.Array:
     b = list(bufs) + [0] * (8 - len(bufs))
     f = list(flags) + [0] * (8 - len(flags))
-    raw = struct.pack("<8Q8QQQ4i", *b, *f, epochs, error, rank, world, channel, emulate)
+    raw = struct.pack("<8Q8QQQ4iQ", *b, *f, epochs, error, rank, world, channel, emulate, multicast)
     lib = native.load_library()
     assert len(raw) == lib.b200_comm_ctx_bytes(), (len(raw), lib.b200_comm_ctx_bytes())
     return ctypes.create_string_buffer(raw, len(raw))
@@ -62,14 +62,35 @@ def _lib():
 class SymmetricArena:
     """One IPC-shared device block per rank with a bump allocator (same sequence on all ranks)."""
 
-    def __init__(self, group, device: torch.device, nbytes: int) -> None:
+    def __init__(self, group, device: torch.device, nbytes: int, provider: str = "ipc") -> None:
         lib = _lib()
         self.group, self.device = group, device
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.nbytes = int(-(-nbytes // (2 << 20)) * (2 << 20))
+        self.multicast = 0
+        self.provider = provider
         assert lib.b200_comm_signal_bytes() + lib.b200_comm_epoch_bytes() + 256 <= HEADER_BYTES
         torch.cuda.set_device(device)
+        if provider == "symm_mem":
+            # PyTorch's symmetric-memory allocator (CUDA VMM + NVLink multicast object) as the memory
+            # provider: same peer-pointer model, plus a multicast address for the NVLS kernels.  Only
+            # allocation / handle exchange is delegated (control plane); all kernels are ours.
+            import torch.distributed._symmetric_memory as symm_mem
+
+            pg = group if group is not None else dist.group.WORLD
+            symm_mem.enable_symm_mem_for_group(pg.group_name)
+            self._symm_tensor = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
+            hdl = symm_mem.rendezvous(self._symm_tensor, pg.group_name)
+            self._symm_handle = hdl
+            self.base = int(self._symm_tensor.data_ptr())
+            self.peer_base = [int(p) for p in hdl.buffer_ptrs]
+            self.multicast = int(hdl.multicast_ptr) if hdl.has_multicast_support(device.type, device.index) else 0
+            self._opened = []
+            self.memory = self._symm_tensor
+            self.memory.zero_()
+            self._finish_init(lib)
+            return
         ptr = ctypes.c_void_p()
         rc = lib.b200_arena_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(ptr))
         if rc != 0:
@@ -96,6 +117,10 @@ class SymmetricArena:
             self.peer_base.append(int(out.value))
             self._opened.append(int(out.value))
         self.memory = _as_tensor(self.base, self.nbytes, device)      # uint8 view of the local arena
+        self._finish_init(lib)
+
+    def _finish_init(self, lib) -> None:
+        group = self.group
         self._cursor = HEADER_BYTES
         sig = lib.b200_comm_signal_bytes()
         self.epochs_ptr = self.base + sig
@@ -107,7 +132,7 @@ class SymmetricArena:
         c = self._ctx.get(channel)
         if c is None:
             c = self._ctx[channel] = _pack_ctx(self.peer_base, self.peer_base, self.epochs_ptr, self.error_ptr,
-                                               self.rank, self.world, channel, 0)
+                                               self.rank, self.world, channel, 0, self.multicast)
         return c
 
     def alloc(self, nbytes: int, align: int = 256) -> int:
@@ -176,7 +201,12 @@ class P2PComm(CommBase):
         if self._arena_bytes is None:
             staging = min(max(grad_bytes, 16 << 20), 256 << 20)
             self._arena_bytes = (int(env) << 20) if env else int(2.3 * grad_bytes) + buffer_bytes + staging + (8 << 20)
-        self.arena = SymmetricArena(self.group, self.device, self._arena_bytes)
+        provider = os.environ.get("B200DDP_ARENA", "symm_mem" if self.algo == "nvls" else "ipc")
+        self.arena = SymmetricArena(self.group, self.device, self._arena_bytes, provider=provider)
+        if self.algo == "nvls" and not self.arena.multicast:
+            import warnings
+
+            warnings.warn("NVLS requested but this box exposes no NVLink multicast: using the two-shot P2P kernel")
 
     def _need_arena(self) -> SymmetricArena:
         if self.arena is None:
@@ -196,7 +226,9 @@ class P2PComm(CommBase):
         lib = _lib()
         if self.algo == "oneshot" and nbytes <= lib.b200_allreduce_oneshot_max_bytes():
             return 1
-        if self.algo in ("twoshot", "nvls"):
+        if self.algo == "nvls":
+            return 3 if (self.arena is not None and self.arena.multicast) else 2
+        if self.algo == "twoshot":
             return 2
         if self.algo == "auto" and nbytes <= self.oneshot_max:
             return 1

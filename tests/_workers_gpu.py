@@ -165,3 +165,54 @@ def fused_wgrad_worker(rank, ws, port, out_dir):
     rec["tc_error"] = native.tc_error_word(dev)
     torch.save(rec, os.path.join(out_dir, f"fused{rank}.pt"))
     d.cleanup()
+
+
+def nvls_worker(rank, ws, port, out_dir):
+    """NVLS (multimem) all-reduce through the symm_mem-provided arena, where the box supports multicast."""
+    d = _init(rank, ws, port)
+    from distributeddataparallel_b200.parallel.p2p import P2PComm
+
+    dev = torch.device("cuda", rank)
+    rec = {"ok": True, "fails": [], "multicast": False, "times": {}}
+    try:
+        comm = P2PComm(None, dev, algo="nvls")
+        comm.reserve(128 << 20)
+    except Exception as e:                      # symm_mem allocator unavailable on this box
+        rec["unavailable"] = repr(e)[:300]
+        torch.save(rec, os.path.join(out_dir, f"nvls{rank}.pt"))
+        d.cleanup()
+        return
+    rec["multicast"] = bool(comm.arena.multicast)
+    rec["provider"] = comm.arena.provider
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    for dtype in (torch.float32, torch.bfloat16):
+        for numel in (4096, 1 << 20, 8_000_000):
+            flat = comm.allocate(numel, dtype, dev)
+            src = torch.randn(numel, generator=g).to(dtype).to(dev)
+            ref = src.float().clone()
+            dist.all_reduce(ref)
+            ref /= ws
+            for algo in ("nvls", "twoshot"):        # both kernels must work on the symm_mem arena
+                comm.algo = algo
+                flat.copy_(src)
+                comm.launch(0, flat, True).wait()
+                torch.cuda.synchronize()
+                gathered = [torch.empty_like(flat) for _ in range(ws)]
+                dist.all_gather(gathered, flat)
+                same = all(torch.equal(gathered[0], t) for t in gathered)
+                tol = 1e-5 if dtype == torch.float32 else 2e-2
+                close = torch.allclose(flat.float(), ref, rtol=tol, atol=tol)
+                if not (same and close):
+                    rec["ok"] = False
+                    rec["fails"].append((str(dtype), numel, algo, same, close))
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize(); dist.barrier()
+                e0.record()
+                for _ in range(10):
+                    comm.launch(0, flat, True).wait()
+                e1.record()
+                torch.cuda.synchronize()
+                rec["times"][(str(dtype), numel, algo)] = e0.elapsed_time(e1) / 10 * 1e3
+    comm.check()
+    torch.save(rec, os.path.join(out_dir, f"nvls{rank}.pt"))
+    d.cleanup()

@@ -48,3 +48,14 @@ def test_fused_wgrad_allreduce(tmp_path):
         rec = torch.load(tmp_path / f"fused{r}.pt")
         assert rec["ok"] and rec["tc_error"] == 0, rec
     print("fused vs unfused ms:", torch.load(tmp_path / "fused0.pt")["times"])
+
+
+def test_nvls_allreduce_where_multicast_exists(tmp_path):
+    n = _n()
+    mp.spawn(W.nvls_worker, args=(n, _port(), str(tmp_path)), nprocs=n, join=True)
+    rec = torch.load(tmp_path / "nvls0.pt")
+    print("nvls:", {k: v for k, v in rec.items() if k != "fails"})
+    if "unavailable" in rec:
+        pytest.skip("symmetric-memory allocator unavailable: " + rec["unavailable"])
+    for r in range(n):
+        assert torch.load(tmp_path / f"nvls{r}.pt")["ok"], torch.load(tmp_path / f"nvls{r}.pt")
