@@ -85,7 +85,7 @@ class SymmetricArena:
             self._symm_handle = hdl
             self.base = int(self._symm_tensor.data_ptr())
             self.peer_base = [int(p) for p in hdl.buffer_ptrs]
-            self.multicast = int(hdl.multicast_ptr) if hdl.has_multicast_support(device.type, device.index) else 0
+            self.multicast = int(hdl.multicast_ptr or 0)       # 0 when the box exposes no NVLink multicast
             self._opened = []
             self.memory = self._symm_tensor
             self.memory.zero_()
