@@ -37,6 +37,9 @@ class TrainStep:
         dev = next(model.parameters()).device
         self.use_graph = bool(cuda_graph) and dev.type == "cuda"
         self._ddp = model if hasattr(model, "reducer") else None
+        import os
+
+        self._nvtx = dev.type == "cuda" and os.environ.get("B200DDP_NVTX", "0") != "0"
 
     def _forward_loss(self, data, target):
         inner = getattr(self.model, "module", self.model)
@@ -46,10 +49,21 @@ class TrainStep:
 
     # -- eager ---------------------------------------------------------------------------
     def _eager(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        nvtx = self._nvtx
         self.optimizer.zero_grad()
+        if nvtx:
+            torch.cuda.nvtx.range_push("b200ddp.forward")
         loss = self._forward_loss(data, target)
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("b200ddp.backward+reduce")
         loss.backward()
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
+            torch.cuda.nvtx.range_push("b200ddp.optimizer")
         self.optimizer.step()
+        if nvtx:
+            torch.cuda.nvtx.range_pop()
         self.eager_steps += 1
         return loss.detach()
 

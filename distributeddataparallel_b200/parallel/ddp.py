@@ -290,6 +290,9 @@ class DistributedDataParallel(nn.Module):
             collectives=dict(self._collectives),
             bucket_launches=self._comm.launches,
         )
+        stats = getattr(self._comm, "stats", None)
+        if stats is not None:
+            d["comm_stats"] = stats()
         return d
 
     @property

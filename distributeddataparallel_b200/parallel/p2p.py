@@ -191,6 +191,12 @@ class P2PComm(CommBase):
         self._staging_bytes = 0
         self._buffer_region = None
         self.bytes_reduced = 0
+        # observability / safety switches
+        self.timing = os.environ.get("B200DDP_COMM_TIMING", "0") != "0"     # device-time every bucket reduction
+        self.debug_check = os.environ.get("B200DDP_DEBUG_COMM", "0") != "0"  # cross-check each bucket against NCCL
+        self.nvtx = os.environ.get("B200DDP_NVTX", "0") != "0"
+        self._timed = []            # (start event, end event, bytes)
+        self.debug_max_err = 0.0
 
     # -- arena ------------------------------------------------------------------------------
     def reserve(self, grad_bytes: int, buffer_bytes: int = 0) -> None:
@@ -249,14 +255,49 @@ class P2PComm(CommBase):
             raise RuntimeError("P2PComm can only reduce buckets that live in the symmetric arena (fp32 / bf16)")
         nbytes = flat.numel() * flat.element_size()
         cur = torch.cuda.current_stream(self.device)
+        capturing = torch.cuda.is_current_stream_capturing()
+        if self.nvtx:
+            torch.cuda.nvtx.range_push(f"b200ddp.bucket{index}.allreduce[{nbytes}B]")
+        expect = None
+        if self.debug_check and not capturing:
+            expect = flat.detach().float().clone()
+            dist.all_reduce(expect, group=self.group)
+            expect /= self.world_size
         ready = torch.cuda.Event()
         ready.record(cur)
         self.stream.wait_event(ready)
+        t0 = None
+        if self.timing and not capturing:
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record(self.stream)
         self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype)
-        done = torch.cuda.Event()
+        done = torch.cuda.Event(enable_timing=t0 is not None)
         done.record(self.stream)
+        if t0 is not None:
+            self._timed.append((t0, done, nbytes))
         self.bytes_reduced += nbytes
+        if self.nvtx:
+            torch.cuda.nvtx.range_pop()
+        if expect is not None:
+            done.synchronize()
+            err = float((flat.float() - expect).abs().max() / expect.abs().max().clamp_min(1e-20))
+            self.debug_max_err = max(self.debug_max_err, err)
+            if err > (1e-2 if flat.dtype == torch.bfloat16 else 1e-4):
+                raise RuntimeError(f"P2P all-reduce of bucket {index} disagrees with NCCL (max rel err {err:.3e})")
         return _EventHandle(done)
+
+    def stats(self) -> dict:
+        """Device-timed per-bucket statistics (needs B200DDP_COMM_TIMING=1; eager steps only)."""
+        out = {"bucket_launches": self.launches, "bytes_reduced": self.bytes_reduced,
+               "debug_max_rel_err_vs_nccl": self.debug_max_err}
+        done = [(a.elapsed_time(b), n) for a, b, n in self._timed if b.query()]
+        if done:
+            ms = sum(t for t, _ in done)
+            nbytes = sum(n for _, n in done)
+            f = 2 * (self.world_size - 1) / self.world_size
+            out.update(timed_buckets=len(done), avg_bucket_allreduce_us=1e3 * ms / len(done),
+                       bus_bandwidth_GBs=nbytes / (ms * 1e-3) * f / 1e9 if ms > 0 else 0.0)
+        return out
 
     def all_reduce_avg_(self, flat: torch.Tensor) -> None:
         """In-place average on the current stream (tensor inside the arena, or staged through it)."""
