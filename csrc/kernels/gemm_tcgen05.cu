@@ -777,6 +777,173 @@ __global__ void __launch_bounds__(256) peer_reduce_wait_kernel(PeerReduce pr, in
   if (threadIdx.x == 0) *pr.epoch = epoch;
 }
 
+
+// =====================================================================================================
+// 2-CTA (cta_group::2) dense GEMM: a cluster of two CTAs on one TPC computes a 256 x BN tile.
+// Each CTA TMA-loads ITS 128 rows of A and ITS half of B (BN/2 rows); the leader CTA's single MMA
+// thread issues tcgen05.mma.cta_group::2 (M = 256), which reads both halves of B through the pair, so
+// per flop each SM pulls half as many operand bytes from L2 as the 1-CTA kernel -- the lever against
+// the L2-bandwidth bound of 128-wide tiles.  Both CTAs' TMA loads complete on the LEADER's full
+// barrier; tcgen05.commit multicasts "stage free" / "accumulator ready" to both CTAs.  Each CTA runs
+// the epilogue for its own 128 rows out of its own TMEM.  TMA-only (dense operands), no split-K.
+// =====================================================================================================
+constexpr int T2_THREADS = 256;      // warp 0: TMA, warp 1: MMA (leader), warp 2: TMEM alloc, warps 4-7: epilogue
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(cta));
+  return r;
+}
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar_cluster) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols));
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols));
+}
+__device__ __forceinline__ void umma_commit2(uint64_t* bar) {   // arrive on this barrier in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+template <bool BF16>
+__device__ __forceinline__ void umma2(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  if (BF16) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+
+template <int AK, int BK_, int BN, bool BF16, int ST>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2_THREADS, 1)
+gemm2_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b) {
+  constexpr int ES = BF16 ? 2 : 4;
+  constexpr int KELEMS = ROW_BYTES / ES;
+  constexpr int UMMA_K = 32 / ES;
+  constexpr int BH = BN / 2;                                  // this CTA's share of the B tile
+  constexpr int A_STAGE = BM * ROW_BYTES, B_STAGE = BH * ROW_BYTES;
+  constexpr uint32_t TMEM_COLS = BN;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t full_bar[ST], empty_bar[ST], accum_bar;
+  __shared__ uint32_t tmem_base_s;
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const uint32_t cta = cluster_ctarank();                     // 0 = leader
+  const int tile_m = blockIdx.x >> 1;
+  const int m0 = tile_m * 2 * BM + (int)cta * BM, n0 = blockIdx.y * BN;
+  const int num_kb = (a.Kd + KELEMS - 1) / KELEMS;
+  const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + ST * A_STAGE;
+
+  if (t == 0) {
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) tmem_alloc2(&tmem_base_s, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                         // peer barriers exist before anyone signals them
+  tc_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+
+  if (warp == 0 && lane == 0) {
+    // ---- TMA producer (both CTAs): my A rows, my half of B; completion lands on the leader's barrier ----
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % ST;
+      if (kb >= ST) mbar_wait(&empty_bar[s], ((kb / ST) - 1) & 1, a.error);
+      const int k0 = kb * KELEMS;
+      const uint32_t bar = map_to_cta(smem_u32(&full_bar[s]), 0);
+      if (cta == 0) mbar_expect_tx(&full_bar[s], 2u * (uint32_t)(A_STAGE + B_STAGE));
+      if (!is_mn(AK)) tma_load_2d_2sm(smem_a + s * A_STAGE, &map_a, k0, m0, bar);
+      else
+        for (int bx = 0; bx < BM / 64; ++bx) tma_load_2d_2sm(smem_a + s * A_STAGE + bx * 8192, &map_a, m0 + bx * 64, k0, bar);
+      const int nb0 = n0 + (int)cta * BH;
+      if (!is_mn(BK_)) tma_load_2d_2sm(smem_b + s * B_STAGE, &map_b, k0, nb0, bar);
+      else
+        for (int bx = 0; bx < BH / 64; ++bx) tma_load_2d_2sm(smem_b + s * B_STAGE + bx * 8192, &map_b, nb0 + bx * 64, k0, bar);
+    }
+  } else if (warp == 1 && lane == 0 && cta == 0) {
+    // ---- MMA issuer: one thread of the leader CTA drives both SMs ----
+    constexpr uint32_t idesc = (1u << 4) | ((BF16 ? 1u : 2u) << 7) | ((BF16 ? 1u : 2u) << 10) |
+                               ((is_mn(AK) ? 1u : 0u) << 15) | ((is_mn(BK_) ? 1u : 0u) << 16) |
+                               ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % ST;
+      mbar_wait(&full_bar[s], (kb / ST) & 1, a.error);
+      tc_fence_after();
+#pragma unroll
+      for (int j = 0; j < KELEMS / UMMA_K; ++j) {
+        const uint64_t da = is_mn(AK) ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
+                                      : make_desc(smem_a + s * A_STAGE + j * 32, 16, 1024, 2u);
+        const uint64_t db = is_mn(BK_) ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
+                                       : make_desc(smem_b + s * B_STAGE + j * 32, 16, 1024, 2u);
+        umma2<BF16>(tmem_d, da, db, idesc, (kb | j) ? 1u : 0u);
+      }
+      umma_commit2(&empty_bar[s]);
+    }
+    umma_commit2(&accum_bar);
+  } else if (warp >= 4) {
+    // ---- epilogue (both CTAs, 4 warps = my 128 accumulator rows) ----
+    mbar_wait(&accum_bar, 0, a.error);
+    tc_fence_after();
+    const int lane_grp = warp & 3;
+    const int row = lane_grp * 32 + lane;
+    float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));
+    constexpr int LDS = BN + 1;
+    const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16);
+#pragma unroll 1
+    for (int c = 0; c < BN / 16; ++c) {
+      float acc[16];
+      tmem_ld16(tmem_row + c * 16, acc);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int gcol = n0 + c * 16 + j;
+        float v = acc[j];
+        if (a.bias != nullptr && gcol < a.N) v += load_bias(a, gcol);
+        stage[row * LDS + c * 16 + j] = v;
+      }
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    float* out_base = a.out;
+    for (int rr = 0; rr < BM / 4; ++rr) {
+      const int r = lane_grp * (BM / 4) + rr, gr = m0 + r;
+      if (gr >= a.M) break;
+#pragma unroll
+      for (int col = lane; col < BN; col += 32) {
+        const int gc = n0 + col;
+        if (gc < a.N) store_out(a, out_base, (size_t)gr * a.ldo + gc, stage[r * LDS + col]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                         // nobody leaves while the pair still talks to it
+  if (warp == 2) tmem_dealloc2(tmem_d, TMEM_COLS);
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -836,10 +1003,65 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
   return static_cast<int>(cudaPeekAtLastError());
 }
 
+
+static bool g_use_2cta = true;
+
+// 2-CTA launch: only for TMA-able dense operands, plain row-major output, no split-K / batching.
+template <int AK, int BK_, int BN, bool BF16>
+static int launch2(const Args& a_in, cudaStream_t st) {
+  constexpr int ES = BF16 ? 2 : 4;
+  constexpr int KELEMS = ROW_BYTES / ES;
+  constexpr int BH = BN / 2;
+  constexpr int ST = BN == 256 ? 6 : 8;                        // 32 KB resp. 24 KB per stage
+  constexpr int smem = ST * (BM + BH) * ROW_BYTES + 1024;
+  static_assert(smem <= 227 * 1024, "pipeline does not fit");
+  static_assert(BM * (BN + 1) * 4 <= ST * (BM + BH) * ROW_BYTES, "epilogue staging does not fit");
+  Args a = a_in;
+  CUtensorMap map_a{}, map_b{};
+  bool ok = true;
+  if (AK == DENSE_K) ok &= make_map(&map_a, a.a, BF16, a.Kd, a.M, a.lda, KELEMS, BM);
+  else ok &= make_map(&map_a, a.a, true, a.M, a.Kd, a.lda, 64, KELEMS);
+  if (BK_ == DENSE_K) ok &= make_map(&map_b, a.b, BF16, a.Kd, a.N, a.ldb, KELEMS, BH);
+  else ok &= make_map(&map_b, a.b, true, a.N, a.Kd, a.ldb, 64, KELEMS);
+  if (!ok) return -1;
+  static bool configured = false;
+  auto kern = gemm2_kernel<AK, BK_, BN, BF16, ST>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  dim3 grid(2 * ceil_div(a.M, 2 * BM), ceil_div(a.N, BN));
+  kern<<<grid, T2_THREADS, smem, st>>>(a, map_a, map_b);
+  return static_cast<int>(cudaPeekAtLastError());
+}
+
+template <int AK, int BK_, bool BF16>
+static int try_2cta(const Args& a, cudaStream_t st) {
+  constexpr bool a_ok = AK == DENSE_K || (AK == DENSE_MN && BF16);
+  constexpr bool b_ok = BK_ == DENSE_K || (BK_ == DENSE_MN && BF16);
+  if constexpr (a_ok && b_ok) {
+    if (!g_use_2cta || !g_use_tma || a.batch > 1 || a.transpose_out || a.stats != nullptr || a.peer.world > 1) return -1;
+    if (a.M < 512 || a.N < 128) return -1;
+    const int bn = a.N >= 256 ? 256 : 128;
+    if ((long long)ceil_div(a.M, 2 * BM) * ceil_div(a.N, bn) < 64) return -1;      // too few cluster tiles: keep 1-CTA + split-K
+    if (bn == 256) return launch2<AK, BK_, 256, BF16>(a, st);
+    return launch2<AK, BK_, 128, BF16>(a, st);
+  } else {
+    return -1;
+  }
+}
+
 template <int AK, int BK_, bool BF16>
 static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int force_bn, cudaStream_t st) {
   constexpr int ES = BF16 ? 2 : 4;
   constexpr int KELEMS = ROW_BYTES / ES;
+  if (a.batch < 1) a.batch = 1;
+  if (a.inner < 1) a.inner = 1;
+  if (!force_bn) {
+    const int rc2 = try_2cta<AK, BK_, BF16>(a, st);
+    if (rc2 >= 0) return rc2;
+  }
   // 256-wide tiles halve the A traffic per flop (L2 bandwidth is what bounds 128x128 tiles); use them
   // when the problem is big enough to still fill the chip
   int bn = force_bn ? force_bn : (a.N <= 32 ? 32 : (a.N <= 64 ? 64 : 128));
@@ -879,6 +1101,8 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
+// Switch the 2-CTA (cta_group::2, 256-row cluster tile) kernel for large dense GEMMs on/off (default on).
+B200_API void b200_gemm_tc_use_2cta(int enabled) { b200::tc::g_use_2cta = enabled != 0; }
 
 // Dense (optionally batched) GEMM; inputs fp32 (TF32 math) or bf16, output fp32 or bf16:
 //   mode 0 (NT): out[M,N] = A[M,K]  * B[N,K]^T      (Linear forward:  x, W)
