@@ -61,6 +61,35 @@ __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ a
   }
 }
 
+// column sums of a tall bf16 matrix into fp32 accumulators (pre-zeroed): rows are split over
+// blockIdx.y so thousands of rows are summed by many CTAs; one atomic per (CTA, column)
+__global__ void __launch_bounds__(256) colsum_bf16_acc_kernel(const __nv_bfloat16* __restrict__ a, float* __restrict__ acc,
+                                                              int M, int N, int rows_per_block) {
+  const int n = blockIdx.x * 64 + (threadIdx.x & 31) * 2;          // two adjacent columns per lane (bf16x2 loads)
+  const int r0 = blockIdx.y * rows_per_block + (threadIdx.x >> 5);
+  const int r1 = min(M, (blockIdx.y + 1) * rows_per_block);
+  __shared__ float sh[8][64];
+  float s0 = 0.f, s1 = 0.f;
+  if (n + 1 < N) {
+    for (int m = r0; m < r1; m += 8) {
+      const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(a + (size_t)m * N + n);
+      s0 += __bfloat162float(v.x);
+      s1 += __bfloat162float(v.y);
+    }
+  } else if (n < N) {
+    for (int m = r0; m < r1; m += 8) s0 += __bfloat162float(a[(size_t)m * N + n]);
+  }
+  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2] = s0;
+  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64 && blockIdx.x * 64 + threadIdx.x < N) {
+    float tot = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) tot += sh[r][threadIdx.x];
+    atomicAdd(acc + blockIdx.x * 64 + threadIdx.x, tot);
+  }
+}
+
 // bf16 variant of colsum (bias gradients of bf16 Linear layers)
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ out,
                                                           int M, int N, int accumulate) {
@@ -113,5 +142,14 @@ B200_API int b200_colsum(const float* a, float* out, int M, int N, int accumulat
 B200_API int b200_colsum_bf16(const void* a, void* out, int M, int N, int accumulate, cudaStream_t stream) {
   colsum_bf16_kernel<<<ceil_div(N, 32), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a),
                                                           static_cast<__nv_bfloat16*>(out), M, N, accumulate);
+  B200_LAUNCH_CHECK();
+}
+
+// acc: fp32 [N], zero on entry; N must be even.  Follow with b200_cast_from_f32 to get a bf16 gradient.
+B200_API int b200_colsum_bf16_acc(const void* a, float* acc, int M, int N, cudaStream_t stream) {
+  if (N % 2) return static_cast<int>(cudaErrorInvalidValue);
+  const int rows_per_block = 256;
+  dim3 grid(ceil_div(N, 64), ceil_div(M, rows_per_block));
+  colsum_bf16_acc_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a), acc, M, N, rows_per_block);
   B200_LAUNCH_CHECK();
 }

@@ -120,6 +120,10 @@ struct Args {
   long long a_s0, a_s1, b_s0, b_s1, o_s0, o_s1;
   int tma_a, tma_b;            // operand is fetched by TMA (dense operands of non-batched calls)
   PeerReduce peer;             // world > 1: fused all-reduce epilogue (needs splits == 1, row-major out)
+  // causal attention structure (batched calls): 1 = output tile is entirely above the diagonal -> skip it
+  // (S = QK^T, dP = dO V^T); 2 = reduction index is the key, only keys <= query row matter (P V, dS K);
+  // 3 = reduction index is the query, only queries >= key row matter (P^T dO, dS^T Q)
+  int causal;
 };
 
 __device__ __forceinline__ void store_out(const Args& a, float* out, size_t idx, float v) {
@@ -383,8 +387,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   const char* b_base = static_cast<const char*>(a.b) + (zo * a.b_s0 + zi * a.b_s1) * ES;
   float* out_base = reinterpret_cast<float*>(reinterpret_cast<char*>(a.out) +
                                              (zo * a.o_s0 + zi * a.o_s1) * (a.out_bf16 ? 2 : 4));
-  const int k_begin = split_z * a.k_per_split;
-  const int k_end = min(a.Kd, k_begin + a.k_per_split);
+  if (a.causal == 1 && n0 >= m0 + BM) return;                      // whole tile masked: nothing reads it
+  int k_begin = split_z * a.k_per_split;
+  int k_end = min(a.Kd, k_begin + a.k_per_split);
+  if (a.causal == 2) k_end = min(k_end, m0 + BM);                   // keys beyond the last query row of the tile are masked
+  if (a.causal == 3) k_begin = max(k_begin, (m0 / KELEMS) * KELEMS);  // queries before the first key row see nothing
   const int num_kb = (k_end - k_begin + KELEMS - 1) / KELEMS;
   const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + STAGES * A_STAGE;   // swizzle is address based
 
@@ -1111,7 +1118,7 @@ B200_API void b200_gemm_tc_use_2cta(int enabled) { b200::tc::g_use_2cta = enable
 // desc = {lda, ldb, ldo, batch, inner, a_s0, a_s1, b_s0, b_s1, o_s0, o_s1} (elements); batch z addresses
 // operand X at X + (z / inner) * x_s0 + (z % inner) * x_s1.  Leading dimensions must keep 16-byte
 // alignment of every row (ld % 4 == 0 for fp32, % 8 for bf16).  flags: bit0 inputs bf16, bit1 output
-// bf16, bit2 bias bf16, bit3 accumulate into out.
+// bf16, bit2 bias bf16, bit3 accumulate into out, bits 4-5 causal structure (see Args::causal).
 B200_API int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, int mode,
                              int flags, const long long* desc, float* workspace, size_t workspace_bytes,
                              unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream) {
@@ -1125,6 +1132,7 @@ B200_API int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void
   a.batch = (int)desc[3]; a.inner = (int)desc[4];
   a.a_s0 = desc[5]; a.a_s1 = desc[6]; a.b_s0 = desc[7]; a.b_s1 = desc[8]; a.o_s0 = desc[9]; a.o_s1 = desc[10];
   a.out_bf16 = (flags >> 1) & 1; a.bias_bf16 = (flags >> 2) & 1; a.accumulate = (flags >> 3) & 1;
+  a.causal = (flags >> 4) & 3;
   a.workspace = workspace; a.counters = counters; a.error = error;
   if (a.lda % vec || a.ldb % vec) return static_cast<int>(cudaErrorInvalidValue);
   if (a.a_s0 % vec || a.a_s1 % vec || a.b_s0 % vec || a.b_s1 % vec) return static_cast<int>(cudaErrorInvalidValue);

@@ -27,10 +27,11 @@ def _bf(t: torch.Tensor) -> int:
 
 def gemm_ex(a, b, out, mode: int, m: int, n: int, k: int, lda: int, ldb: int, ldo: int,
             bias: Optional[torch.Tensor] = None, batch: int = 1, inner: int = 1,
-            strides=(0, 0, 0, 0, 0, 0), accumulate: bool = False) -> None:
+            strides=(0, 0, 0, 0, 0, 0), accumulate: bool = False, causal: int = 0) -> None:
     """out = op(a) @ op(b) on the tcgen05 kernel (see b200_gemm_tc_ex for modes / descriptors)."""
     assert a.dtype == b.dtype and a.dtype in (torch.float32, torch.bfloat16), (a.dtype, b.dtype)
-    flags = _bf(a) | (_bf(out) << 1) | ((_bf(bias) if bias is not None else 0) << 2) | (int(accumulate) << 3)
+    flags = (_bf(a) | (_bf(out) << 1) | ((_bf(bias) if bias is not None else 0) << 2) | (int(accumulate) << 3)
+             | (int(causal) << 4))
     desc = _ll11(lda, ldb, ldo, batch, inner, *strides)
     s = scratch(a.device)
     _call("b200_gemm_tc_ex", _ptr(a), _ptr(b), _ptr(out), _ptr(bias), _i(m), _i(n), _i(k), _i(mode), _i(flags),
@@ -72,7 +73,11 @@ class _LinearTC(torch.autograd.Function):
             gemm_ex(dy2, x2, dw, 2, n, k, m, n, k, k)                   # dW = dy^T @ x
         if ctx.params[1] is not None and ctx.needs_input_grad[2]:
             db, _ = _grad_target(ctx.params[1], ctx.slots[1], ctx.params[1])
-            if _bf(dy2):
+            if _bf(dy2) and m >= 1024 and n % 2 == 0:
+                acc = torch.zeros(n, dtype=torch.float32, device=dy.device)
+                _call("b200_colsum_bf16_acc", _ptr(dy2), _ptr(acc), _i(m), _i(n), _stream())
+                _call("b200_cast_from_f32", _ptr(acc), _ptr(db), _sz(n), _i(0), _i(1), _stream())
+            elif _bf(dy2):
                 _call("b200_colsum_bf16", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
             else:
                 _call("b200_colsum", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
@@ -160,12 +165,12 @@ class _CausalSelfAttention(torch.autograd.Function):
         row = 3 * hd                                                              # pitch of one token's qkv row
         # S[z] = Q[z] K[z]^T      (batch z = (b, h): offset b*T*row + h*D)
         gemm_ex(q, k, p, 0, t, t, d, row, row, t, batch=z, inner=heads,
-                strides=(t * row, d, t * row, d, heads * t * t, t * t))
+                strides=(t * row, d, t * row, d, heads * t * t, t * t), causal=1)
         _call("b200_causal_softmax_fwd", _ptr(p), _i(t), _sz(z * t), ctypes.c_float(scale), _i(_bf(p)), _stream())
         out = torch.empty((b, t, hd), dtype=qkv.dtype, device=qkv.device)
         # O[z] = P[z] V[z]        (written into [B, T, H, D] layout: pitch hd, offset b*T*hd + h*D)
         gemm_ex(p, v, out, 1, t, d, t, t, row, hd, batch=z, inner=heads,
-                strides=(heads * t * t, t * t, t * row, d, t * hd, d))
+                strides=(heads * t * t, t * t, t * row, d, t * hd, d), causal=2)
         ctx.save_for_backward(qkv, p)
         ctx.cfg = (b, t, heads, d, scale)
         return out
@@ -181,15 +186,19 @@ class _CausalSelfAttention(torch.autograd.Function):
         dq, dk, dv = dqkv.view(-1)[0:], dqkv.view(-1)[hd:], dqkv.view(-1)[2 * hd:]
         sq = (heads * t * t, t * t)
         # dV[z] = P^T dO
-        gemm_ex(p, dout, dv, 2, t, d, t, t, hd, row, batch=z, inner=heads, strides=(*sq, t * hd, d, t * row, d))
+        gemm_ex(p, dout, dv, 2, t, d, t, t, hd, row, batch=z, inner=heads, strides=(*sq, t * hd, d, t * row, d),
+                causal=3)
         # dP[z] = dO V^T
         dp = torch.empty_like(p)
-        gemm_ex(dout, v, dp, 0, t, t, d, hd, row, t, batch=z, inner=heads, strides=(t * hd, d, t * row, d, *sq))
+        gemm_ex(dout, v, dp, 0, t, t, d, hd, row, t, batch=z, inner=heads, strides=(t * hd, d, t * row, d, *sq),
+                causal=1)
         _call("b200_causal_softmax_bwd", _ptr(p), _ptr(dp), _i(t), _sz(z * t), ctypes.c_float(scale), _i(_bf(p)),
               _stream())
         # dQ[z] = dS K ;  dK[z] = dS^T Q
-        gemm_ex(dp, k, dq, 1, t, d, t, t, row, row, batch=z, inner=heads, strides=(*sq, t * row, d, t * row, d))
-        gemm_ex(dp, q, dk, 2, t, d, t, t, row, row, batch=z, inner=heads, strides=(*sq, t * row, d, t * row, d))
+        gemm_ex(dp, k, dq, 1, t, d, t, t, row, row, batch=z, inner=heads, strides=(*sq, t * row, d, t * row, d),
+                causal=2)
+        gemm_ex(dp, q, dk, 2, t, d, t, t, row, row, batch=z, inner=heads, strides=(*sq, t * row, d, t * row, d),
+                causal=3)
         return dqkv, None
 
 

@@ -98,6 +98,7 @@ int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, flo
 int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
 int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream);
 int b200_colsum_bf16(const void* a, void* out, int M, int N, int accumulate, cudaStream_t stream);
+int b200_colsum_bf16_acc(const void* a, float* acc, int M, int N, cudaStream_t stream);   /* tall matrices: fp32 atomics */
 
 /* ---- fused multi-tensor optimizers (optim.SGD at REF:41,53) -------------------------
  * recs: device array of {float* p, g, s0, s1; int64 n; int64 dtype (0 fp32, 1 bf16 p/g)}; chunks: device array of

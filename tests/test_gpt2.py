@@ -74,3 +74,24 @@ def test_gpt2_ddp_graph_step_bf16():
     losses = [float(step(idx, tgt)) for _ in range(12)]
     assert step.captured and step.replays >= 8
     assert losses[-1] < losses[0] - 0.2, losses
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 5e-3), (torch.bfloat16, 4e-2)])
+def test_causal_attention_multi_tile_matches_sdpa(dtype, tol):
+    """T = 384 spans three 128-row tiles: exercises the causal tile skipping of all six attention GEMMs."""
+    from distributeddataparallel_b200.ops import native_tf
+
+    torch.manual_seed(0)
+    b, t, h, dh = 2, 384, 4, 64
+    qkv64 = torch.randn(b, t, 3 * h * dh, dtype=torch.float64)
+    qkv = qkv64.to("cuda", dtype).requires_grad_(True)
+    out = native_tf.causal_self_attention(qkv, h)
+    ref_in = qkv64.clone().requires_grad_(True)
+    q, k, v = ref_in.view(b, t, 3, h, dh).permute(2, 0, 3, 1, 4)
+    ref = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(b, t, h * dh)
+    assert _rel(out.cpu(), ref) < tol, _rel(out.cpu(), ref)
+    g = torch.randn(b, t, h * dh, dtype=torch.float64)
+    out.backward(g.to("cuda", dtype))
+    ref.backward(g)
+    assert _rel(qkv.grad.cpu(), ref_in.grad) < 2 * tol, _rel(qkv.grad.cpu(), ref_in.grad)
