@@ -951,6 +951,163 @@ gemm2_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __gr
   if (warp == 2) tmem_dealloc2(tmem_d, TMEM_COLS);
 }
 
+
+// -----------------------------------------------------------------------------------------------------
+// Persistent variant of the 2-CTA kernel: one cluster per TPC loops over output tiles; the accumulator
+// is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i (TMEM -> registers -> global,
+// no shared-memory staging) overlaps the TMA/MMA main loop of tile i+1.
+//   full/empty[ST]   : smem ring, continuous across tiles (as in gemm2_kernel)
+//   tmem_full[2]     : MMA -> epilogue, multicast commit to both CTAs
+//   tmem_empty[2]    : epilogue -> MMA, lives in the LEADER, 4 warps x 2 CTAs arrive (peer arrives remotely)
+// -----------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
+
+template <int AK, int BK_, int BN, bool BF16, int ST>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2_THREADS, 1)
+gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+              int tiles_n, int num_tiles) {
+  constexpr int ES = BF16 ? 2 : 4;
+  constexpr int KELEMS = ROW_BYTES / ES;
+  constexpr int UMMA_K = 32 / ES;
+  constexpr int BH = BN / 2;
+  constexpr int A_STAGE = BM * ROW_BYTES, B_STAGE = BH * ROW_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BN;                      // two accumulator buffers
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ __align__(8) uint64_t full_bar[ST], empty_bar[ST], tmem_full[2], tmem_empty[2];
+  __shared__ uint32_t tmem_base_s;
+
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  const uint32_t cta = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int num_kb = (a.Kd + KELEMS - 1) / KELEMS;
+  const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + ST * A_STAGE;
+
+  if (t == 0) {
+    for (int s = 0; s < ST; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full[b], 1);
+      mbar_init(&tmem_empty[b], 8);                          // 4 epilogue warps in each of the 2 CTAs
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) tmem_alloc2(&tmem_base_s, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+
+  if (warp == 0 && lane == 0) {
+    // ---- TMA producer ----
+    int kc = 0;                                               // running k-block counter across tiles
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m0 = (tile / tiles_n) * 2 * BM + (int)cta * BM, n0 = (tile % tiles_n) * BN;
+      for (int kb = 0; kb < num_kb; ++kb, ++kc) {
+        const int s = kc % ST;
+        if (kc >= ST) mbar_wait(&empty_bar[s], ((kc / ST) - 1) & 1, a.error);
+        const int k0 = kb * KELEMS;
+        const uint32_t bar = map_to_cta(smem_u32(&full_bar[s]), 0);
+        if (cta == 0) mbar_expect_tx(&full_bar[s], 2u * (uint32_t)(A_STAGE + B_STAGE));
+        if (!is_mn(AK)) tma_load_2d_2sm(smem_a + s * A_STAGE, &map_a, k0, m0, bar);
+        else
+          for (int bx = 0; bx < BM / 64; ++bx) tma_load_2d_2sm(smem_a + s * A_STAGE + bx * 8192, &map_a, m0 + bx * 64, k0, bar);
+        const int nb0 = n0 + (int)cta * BH;
+        if (!is_mn(BK_)) tma_load_2d_2sm(smem_b + s * B_STAGE, &map_b, k0, nb0, bar);
+        else
+          for (int bx = 0; bx < BH / 64; ++bx) tma_load_2d_2sm(smem_b + s * B_STAGE + bx * 8192, &map_b, nb0 + bx * 64, k0, bar);
+      }
+    }
+  } else if (warp == 1 && lane == 0 && cta == 0) {
+    // ---- MMA issuer (leader) ----
+    constexpr uint32_t idesc = (1u << 4) | ((BF16 ? 1u : 2u) << 7) | ((BF16 ? 1u : 2u) << 10) |
+                               ((is_mn(AK) ? 1u : 0u) << 15) | ((is_mn(BK_) ? 1u : 0u) << 16) |
+                               ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+    int kc = 0, it = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+      const int buf = it & 1;
+      if (it >= 2) mbar_wait(&tmem_empty[buf], ((it >> 1) - 1) & 1, a.error);   // epilogues drained this buffer
+      tc_fence_after();
+      const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+      for (int kb = 0; kb < num_kb; ++kb, ++kc) {
+        const int s = kc % ST;
+        mbar_wait(&full_bar[s], (kc / ST) & 1, a.error);
+        tc_fence_after();
+#pragma unroll
+        for (int j = 0; j < KELEMS / UMMA_K; ++j) {
+          const uint64_t da = is_mn(AK) ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
+                                        : make_desc(smem_a + s * A_STAGE + j * 32, 16, 1024, 2u);
+          const uint64_t db = is_mn(BK_) ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
+                                         : make_desc(smem_b + s * B_STAGE + j * 32, 16, 1024, 2u);
+          umma2<BF16>(acc, da, db, idesc, (kb | j) ? 1u : 0u);
+        }
+        umma_commit2(&empty_bar[s]);
+      }
+      umma_commit2(&tmem_full[buf]);
+    }
+  } else if (warp >= 4) {
+    // ---- epilogue: TMEM -> registers -> global, 16 columns at a time ----
+    const int lane_grp = warp & 3;
+    const int row = lane_grp * 32 + lane;
+    const uint32_t empty_leader0 = map_to_cta(smem_u32(&tmem_empty[0]), 0);
+    const uint32_t empty_leader1 = map_to_cta(smem_u32(&tmem_empty[1]), 0);
+    int it = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+      const int buf = it & 1;
+      const int m0 = (tile / tiles_n) * 2 * BM + (int)cta * BM, n0 = (tile % tiles_n) * BN;
+      mbar_wait(&tmem_full[buf], (it >> 1) & 1, a.error);
+      tc_fence_after();
+      const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(buf * BN);
+      const int gr = m0 + row;
+#pragma unroll 1
+      for (int c = 0; c < BN / 16; ++c) {
+        float acc[16];
+        tmem_ld16(tmem_row + c * 16, acc);
+        const int gc0 = n0 + c * 16;
+        if (gr >= a.M || gc0 >= a.N) continue;
+        if (a.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (gc0 + j < a.N) acc[j] += load_bias(a, gc0 + j);
+        }
+        const size_t o = (size_t)gr * a.ldo + gc0;
+        const bool full = gc0 + 15 < a.N && !a.accumulate;
+        if (full && a.out_bf16 && ((o & 7) == 0)) {
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+            w[j] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.out) + o);
+          dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+          dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        } else if (full && !a.out_bf16 && ((o & 3) == 0)) {
+          float4* dst = reinterpret_cast<float4*>(a.out + o);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dst[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (gc0 + j < a.N) store_out(a, a.out, o + j, acc[j]);
+        }
+      }
+      // this warp is done reading buffer `buf`: tell the leader's MMA thread
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(buf ? empty_leader1 : empty_leader0);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc2(tmem_d, TMEM_COLS);
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -1011,7 +1168,7 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
 }
 
 
-static bool g_use_2cta = true;
+static int g_use_2cta = 2;       // 0 off, 1 one tile per cluster, 2 persistent with double-buffered TMEM
 
 // 2-CTA launch: only for TMA-able dense operands, plain row-major output, no split-K / batching.
 template <int AK, int BK_, int BN, bool BF16>
@@ -1037,6 +1194,19 @@ static int launch2(const Args& a_in, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
+  }
+  if (g_use_2cta >= 2) {
+    static bool configured_p = false;
+    auto kp = gemm2p_kernel<AK, BK_, BN, BF16, ST>;
+    if (!configured_p) {
+      cudaError_t e = cudaFuncSetAttribute(kp, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      configured_p = true;
+    }
+    const int tiles_n = ceil_div(a.N, BN), num_tiles = ceil_div(a.M, 2 * BM) * tiles_n;
+    const int clusters = min(num_tiles, kNumSMs / 2);
+    kp<<<dim3(2 * clusters), T2_THREADS, smem, st>>>(a, map_a, map_b, tiles_n, num_tiles);
+    return static_cast<int>(cudaPeekAtLastError());
   }
   dim3 grid(2 * ceil_div(a.M, 2 * BM), ceil_div(a.N, BN));
   kern<<<grid, T2_THREADS, smem, st>>>(a, map_a, map_b);
@@ -1108,8 +1278,8 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
-// Switch the 2-CTA (cta_group::2, 256-row cluster tile) kernel for large dense GEMMs on/off (default on).
-B200_API void b200_gemm_tc_use_2cta(int enabled) { b200::tc::g_use_2cta = enabled != 0; }
+// 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_use_2cta(int mode) { b200::tc::g_use_2cta = mode; }   // 0 off, 1 simple, 2 persistent
 
 // Dense (optionally batched) GEMM; inputs fp32 (TF32 math) or bf16, output fp32 or bf16:
 //   mode 0 (NT): out[M,N] = A[M,K]  * B[N,K]^T      (Linear forward:  x, W)

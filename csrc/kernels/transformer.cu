@@ -57,6 +57,46 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
   for (int j = threadIdx.x; j < 2 * D; j += blockDim.x) sh[j] = 0.f;
   __syncthreads();
   const int warps = blockDim.x >> 5, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (D <= 1024) {
+    // a lane always serves columns lane, lane+32, ...: keep its dgamma/dbeta partials in registers over
+    // all rows of the warp and touch shared memory once at the end
+    float pg[32], pb[32];
+#pragma unroll
+    for (int q = 0; q < 32; ++q) pg[q] = pb[q] = 0.f;
+    for (int row = blockIdx.x * warps + w; row < M; row += gridDim.x * warps) {
+      const T* xr = x + (size_t)row * D;
+      const T* gr = dy + (size_t)row * D;
+      const float mu = mean[row], rs = rstd[row];
+      float a = 0.f, b = 0.f;
+      for (int j = lane; j < D; j += 32) {
+        const float g = to_f(gr[j]) * to_f(gamma[j]);
+        a += g;
+        b += g * (to_f(xr[j]) - mu) * rs;
+      }
+      a = warp_sum(a) / D;
+      b = warp_sum(b) / D;
+      T* dr = dx + (size_t)row * D;
+#pragma unroll
+      for (int q = 0; q < 32; ++q) {
+        const int j = lane + q * 32;
+        if (j < D) {
+          const float go = to_f(gr[j]);
+          const float xh = (to_f(xr[j]) - mu) * rs;
+          dr[j] = from_f<T>(rs * (go * to_f(gamma[j]) - a - xh * b));
+          pg[q] += go * xh;
+          pb[q] += go;
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 32; ++q) {
+      const int j = lane + q * 32;
+      if (j < D) {
+        atomicAdd(&sh[j], pg[q]);
+        atomicAdd(&sh[D + j], pb[q]);
+      }
+    }
+  } else
   for (int row = blockIdx.x * warps + w; row < M; row += gridDim.x * warps) {
     const T* xr = x + (size_t)row * D;
     const T* gr = dy + (size_t)row * D;
@@ -139,7 +179,9 @@ __global__ void __launch_bounds__(256) causal_softmax_fwd_kernel(T* __restrict__
   float se = 0.f;
   for (int j = lane; j <= i; j += 32) se += __expf(to_f(r[j]) * scale - mx);
   const float inv = 1.f / warp_sum(se);
-  for (int j = lane; j < T_len; j += 32) r[j] = from_f<T>(j <= i ? __expf(to_f(r[j]) * scale - mx) * inv : 0.f);
+  // columns past the diagonal 128-tile are never read (the P.V / dS.K GEMMs stop at the tile edge)
+  const int j_end = min(T_len, (i / 128 + 1) * 128);
+  for (int j = lane; j < j_end; j += 32) r[j] = from_f<T>(j <= i ? __expf(to_f(r[j]) * scale - mx) * inv : 0.f);
 }
 template <typename T>
 __global__ void __launch_bounds__(256) causal_softmax_bwd_kernel(const T* __restrict__ p, T* __restrict__ dp, int T_len,
@@ -153,7 +195,8 @@ __global__ void __launch_bounds__(256) causal_softmax_bwd_kernel(const T* __rest
   float dot = 0.f;
   for (int j = lane; j <= i; j += 32) dot += to_f(pr[j]) * to_f(dr[j]);
   dot = warp_sum(dot);
-  for (int j = lane; j < T_len; j += 32) dr[j] = from_f<T>(j <= i ? scale * to_f(pr[j]) * (to_f(dr[j]) - dot) : 0.f);
+  const int j_end = min(T_len, (i / 128 + 1) * 128);
+  for (int j = lane; j < j_end; j += 32) dr[j] = from_f<T>(j <= i ? scale * to_f(pr[j]) * (to_f(dr[j]) - dot) : 0.f);
 }
 
 // ---- embedding: out[b, t, :] = wte[idx[b, t], :] + wpe[t, :] ---------------------------------------------

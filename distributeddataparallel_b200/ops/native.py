@@ -14,6 +14,7 @@ gradient already in place (SURVEY.md K18/K19 eliminated).
 from __future__ import annotations
 
 import ctypes
+import os
 import struct
 from typing import Dict, List, Optional, Sequence
 
@@ -37,6 +38,10 @@ def load_library():
     lib = ctypes.CDLL(str(path))
     for name in ("b200_optim_chunk_elems", "b200_optim_rec_bytes"):
         getattr(lib, name).restype = ctypes.c_int
+    if "B200DDP_2CTA" in os.environ:       # 0 off, 1 one tile per cluster, 2 persistent (library default)
+        lib.b200_gemm_tc_use_2cta(ctypes.c_int(int(os.environ["B200DDP_2CTA"])))
+    if "B200DDP_TMA" in os.environ:
+        lib.b200_gemm_tc_use_tma(ctypes.c_int(int(os.environ["B200DDP_TMA"])))
     _lib = lib
     return lib
 
