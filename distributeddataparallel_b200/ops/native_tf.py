@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 from typing import Optional
 
 import torch
@@ -148,6 +149,24 @@ def gelu(x):
 
 
 # ---------------------------------------------------------------------------------------------
+_FUSED_ATTENTION = os.environ.get("B200DDP_FUSED_ATTENTION", "1") != "0"
+
+
+def set_fused_attention(enabled: bool) -> None:
+    global _FUSED_ATTENTION
+    _FUSED_ATTENTION = bool(enabled)
+
+
+def _try_call(name: str, *args) -> int:
+    """Like ``_call`` but hands 801 (shape / descriptor not supported) back to the caller."""
+    rc = getattr(native.load_library(), name)(*args)
+    if rc not in (0, 801):
+        raise RuntimeError(f"{name} failed: CUDA error {rc}")
+    if rc == 0:
+        native._launches += 1
+    return rc
+
+
 class _CausalSelfAttention(torch.autograd.Function):
     """qkv: [B, T, 3*H*D] (the fused projection output)  ->  [B, T, H*D]."""
 
@@ -159,6 +178,18 @@ class _CausalSelfAttention(torch.autograd.Function):
         d = hd // heads
         z = b * heads
         scale = 1.0 / math.sqrt(d)
+        ctx.fused = False
+        if _FUSED_ATTENTION and d == 64 and qkv.dtype == torch.bfloat16:
+            # one kernel: scores stay in TMEM / shared memory (csrc/kernels/attention_tcgen05.cu)
+            out = torch.empty((b, t, hd), dtype=qkv.dtype, device=qkv.device)
+            lse = torch.empty((z, t), dtype=torch.float32, device=qkv.device)
+            rc = _try_call("b200_attention_fwd", _ptr(qkv), _ptr(out), _ptr(lse), _i(b), _i(heads), _i(t),
+                           _ptr(scratch(qkv.device).error), _stream())
+            if rc == 0:
+                ctx.fused = True
+                ctx.save_for_backward(qkv, out, lse)
+                ctx.cfg = (b, t, heads, d, scale)
+                return out
         es = qkv.element_size()
         q, k, v = qkv.view(-1)[0:], qkv.view(-1)[hd:], qkv.view(-1)[2 * hd:]      # same buffer, column offsets
         p = torch.empty((z, t, t), dtype=qkv.dtype, device=qkv.device)
@@ -177,8 +208,17 @@ class _CausalSelfAttention(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dout):
-        qkv, p = ctx.saved_tensors
         b, t, heads, d, scale = ctx.cfg
+        if ctx.fused:
+            qkv, out, lse = ctx.saved_tensors
+            dout = dout.contiguous()
+            dqkv = torch.empty_like(qkv)
+            delta = torch.empty_like(lse)
+            dq32 = torch.empty((b * t, heads * d), dtype=torch.float32, device=qkv.device)
+            _call("b200_attention_bwd", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dq32), _ptr(dqkv),
+                  _i(b), _i(heads), _i(t), _ptr(scratch(qkv.device).error), _stream(), kernels=4)
+            return dqkv, None
+        qkv, p = ctx.saved_tensors
         hd, z, row = heads * d, b * heads, 3 * heads * d
         dout = dout.contiguous()
         q, k, v = qkv.view(-1)[0:], qkv.view(-1)[hd:], qkv.view(-1)[2 * hd:]

@@ -152,6 +152,13 @@ int b200_gelu_fwd(const void* x, void* y, size_t n, int is_bf16, cudaStream_t st
 int b200_gelu_bwd(const void* x, const void* dy, void* dx, size_t n, int is_bf16, cudaStream_t st);
 int b200_causal_softmax_fwd(void* s, int T_len, size_t rows, float scale, int is_bf16, cudaStream_t st);
 int b200_causal_softmax_bwd(const void* p, void* dp, int T_len, size_t rows, float scale, int is_bf16, cudaStream_t st);
+/* Fused causal self-attention, head dimension 64, bf16 (csrc/kernels/attention_tcgen05.cu): reads q|k|v in place
+ * from qkv[B*T, 3*H*64]; out[B*T, H*64]; lse[B*H, T] (log2 domain) feeds the backward.  The backward needs two
+ * fp32 scratch arrays: delta[B*H*T] and dq32[B*T*H*64].  801 = TMA descriptor unavailable (use the GEMM path).
+ * No counterpart on the reference's path (dpp.py trains a CNN); stock PyTorch uses a flash-attention library. */
+int b200_attention_fwd(const void* qkv, void* out, float* lse, int B, int H, int T, unsigned* error, cudaStream_t st);
+int b200_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                       float* dq32, void* dqkv, int B, int H, int T, unsigned* error, cudaStream_t st);
 int b200_embedding_fwd(const long long* idx, const void* wte, const void* wpe, void* out, size_t rows, int T_len,
                        int D, int is_bf16, cudaStream_t st);
 int b200_embedding_bwd(const long long* idx, const void* dout, float* dwte_acc, float* dwpe_acc, size_t rows,
