@@ -124,6 +124,11 @@ struct Args {
   // (S = QK^T, dP = dO V^T); 2 = reduction index is the key, only keys <= query row matter (P V, dS K);
   // 3 = reduction index is the query, only queries >= key row matter (P^T dO, dS^T Q)
   int causal;
+  // fused epilogue (persistent 2-CTA kernel, bf16 output; aux / aux_out are bf16 [M, N] with pitch ldo):
+  //   1: aux_out = v, out = gelu(v)      2: out = v * gelu'(aux)      3: out = v + aux       (v = acc + bias)
+  int epi;
+  const void* aux;
+  void* aux_out;
 };
 
 __device__ __forceinline__ void store_out(const Args& a, float* out, size_t idx, float v) {
@@ -141,6 +146,37 @@ __device__ __forceinline__ float load_bias(const Args& a, int i) {
 __host__ __device__ constexpr uint32_t make_idesc(bool bf16, bool a_mn, bool b_mn, int n) {
   return (1u << 4) | ((bf16 ? 1u : 2u) << 7) | ((bf16 ? 1u : 2u) << 10) | ((a_mn ? 1u : 0u) << 15) |
          ((b_mn ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  return 0.5f * x * (1.f + tanhf(u));
+}
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+  const float t = tanhf(u);
+  const float du = 0.7978845608028654f * (1.f + 3.f * 0.044715f * x * x);
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+}
+__device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* p, float (&v)[16]) {
+  const uint4 lo = reinterpret_cast<const uint4*>(p)[0], hi = reinterpret_cast<const uint4*>(p)[1];
+  const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&lo);
+  const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&hi);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 x = __bfloat1622float2(a[j]), y = __bfloat1622float2(b[j]);
+    v[2 * j] = x.x; v[2 * j + 1] = x.y; v[8 + 2 * j] = y.x; v[8 + 2 * j + 1] = y.y;
+  }
+}
+__device__ __forceinline__ void store_bf16x16(__nv_bfloat16* p, const float (&v)[16]) {
+  uint32_t w[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+    w[j] = *reinterpret_cast<const uint32_t*>(&h);
+  }
+  reinterpret_cast<uint4*>(p)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  reinterpret_cast<uint4*>(p)[1] = make_uint4(w[4], w[5], w[6], w[7]);
 }
 
 // ---- operand gathers ---------------------------------------------------------------------------
@@ -983,16 +1019,20 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
         }
         const size_t o = (size_t)gr * a.ldo + gc0;
         const bool full = gc0 + 15 < a.N && !a.accumulate;
-        if (full && a.out_bf16 && ((o & 7) == 0)) {
-          uint32_t w[8];
+        if (a.epi != 0) {                                  // host guarantees bf16 output, N % 16 == 0, ldo % 8 == 0
+          if (a.epi == 1) {
+            store_bf16x16(reinterpret_cast<__nv_bfloat16*>(a.aux_out) + o, acc);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const __nv_bfloat162 h = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
-            w[j] = *reinterpret_cast<const uint32_t*>(&h);
+            for (int j = 0; j < 16; ++j) acc[j] = gelu_tanh(acc[j]);
+          } else {
+            float x[16];
+            load_bf16x16(reinterpret_cast<const __nv_bfloat16*>(a.aux) + o, x);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) acc[j] = a.epi == 2 ? acc[j] * gelu_tanh_grad(x[j]) : acc[j] + x[j];
           }
-          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.out) + o);
-          dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-          dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+          store_bf16x16(reinterpret_cast<__nv_bfloat16*>(a.out) + o, acc);
+        } else if (full && a.out_bf16 && ((o & 7) == 0)) {
+          store_bf16x16(reinterpret_cast<__nv_bfloat16*>(a.out) + o, acc);
         } else if (full && !a.out_bf16 && ((o & 3) == 0)) {
           float4* dst = reinterpret_cast<float4*>(a.out + o);
 #pragma unroll
@@ -1100,10 +1140,16 @@ static int try_2cta(const Args& a, cudaStream_t st) {
   constexpr bool a_ok = AK == DENSE_K || (AK == DENSE_MN && BF16);
   constexpr bool b_ok = BK_ == DENSE_K || (BK_ == DENSE_MN && BF16);
   if constexpr (a_ok && b_ok) {
+    if (a.epi != 0 && (g_use_2cta < 2 || !a.out_bf16 || a.N % 16 || a.ldo % 8 || a.accumulate)) return -1;
     if (!g_use_2cta || !g_use_tma || a.batch > 1 || a.transpose_out || a.stats != nullptr || a.peer.world > 1) return -1;
     if (a.M < 512 || a.N < 128) return -1;
-    const int bn = a.N >= 256 ? 256 : 128;
-    if ((long long)ceil_div(a.M, 2 * BM) * ceil_div(a.N, bn) < 64) return -1;      // too few cluster tiles: keep 1-CTA + split-K
+    // 256 x 256 or 256 x 128 cluster tiles: whichever needs less time on 74 clusters (rounds x tile width);
+    // ties go to the wider tile (half the A traffic per flop)
+    const long long rows = ceil_div(a.M, 2 * BM), t256 = rows * ceil_div(a.N, 256), t128 = rows * ceil_div(a.N, 128);
+    const long long clusters = kNumSMs / 2;
+    const long long c256 = ((t256 + clusters - 1) / clusters) * 256, c128 = ((t128 + clusters - 1) / clusters) * 128;
+    const int bn = (a.N >= 256 && c256 <= c128) ? 256 : 128;
+    if ((bn == 256 ? t256 : t128) < 24) return -1;           // too few cluster tiles: keep 1-CTA + split-K
     if (bn == 256) return launch2<AK, BK_, 256, BF16>(a, st);
     return launch2<AK, BK_, 128, BF16>(a, st);
   } else {
@@ -1121,6 +1167,7 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
     const int rc2 = try_2cta<AK, BK_, BF16>(a, st);
     if (rc2 >= 0) return rc2;
   }
+  if (a.epi != 0) return static_cast<int>(cudaErrorNotSupported);   // fused epilogues exist only in the persistent kernel
   // 256-wide tiles halve the A traffic per flop (L2 bandwidth is what bounds 128x128 tiles); use them
   // when the problem is big enough to still fill the chip
   int bn = force_bn ? force_bn : (a.N <= 32 ? 32 : (a.N <= 64 ? 64 : 128));
@@ -1195,6 +1242,33 @@ B200_API int b200_gemm_tc_ex(const void* A, const void* B, void* out, const void
   if (mode == 1) { B200_GEMM_MODE(DENSE_K, DENSE_MN); }
   if (mode == 2) { B200_GEMM_MODE(DENSE_MN, DENSE_MN); }
 #undef B200_GEMM_MODE
+  return static_cast<int>(cudaErrorInvalidValue);
+}
+
+// b200_gemm_tc_ex with a fused epilogue (see Args::epi): epi 1 = GELU forward (aux_out receives the pre-activation),
+// 2 = GELU backward (out = result * gelu'(aux)), 3 = residual add (out = result + aux).  bf16 output only; returns
+// cudaErrorNotSupported (801) when the shape does not run on the persistent 2-CTA kernel -- the caller then uses the
+// unfused kernels.
+B200_API int b200_gemm_tc_epi(const void* A, const void* B, void* out, const void* bias, const void* aux, void* aux_out,
+                              int epi, int M, int N, int K, int mode, int flags, const long long* desc, float* workspace,
+                              size_t workspace_bytes, unsigned* counters, int max_counters, unsigned* error,
+                              cudaStream_t stream) {
+  const bool bf16 = flags & 1;
+  if (!bf16 || !((flags >> 1) & 1) || epi < 1 || epi > 3) return static_cast<int>(cudaErrorNotSupported);
+  if (!ptr16(A) || !ptr16(B) || !ptr16(out) || (epi == 1 ? !ptr16(aux_out) || !aux_out : !ptr16(aux) || !aux))
+    return static_cast<int>(cudaErrorInvalidValue);
+  Args a{};
+  a.a = A; a.b = B; a.out = static_cast<float*>(out); a.bias = static_cast<const float*>(bias);
+  a.M = M; a.N = N; a.Kd = K;
+  a.lda = desc[0]; a.ldb = desc[1]; a.ldo = desc[2];
+  a.batch = 1; a.inner = 1;
+  a.out_bf16 = 1; a.bias_bf16 = (flags >> 2) & 1;
+  a.workspace = workspace; a.counters = counters; a.error = error;
+  a.epi = epi; a.aux = aux; a.aux_out = aux_out;
+  if (a.lda % 8 || a.ldb % 8) return static_cast<int>(cudaErrorInvalidValue);
+  if (mode == 0) return dispatch_bn<DENSE_K, DENSE_K, true>(a, workspace_bytes, max_counters, 0, stream);
+  if (mode == 1) return dispatch_bn<DENSE_K, DENSE_MN, true>(a, workspace_bytes, max_counters, 0, stream);
+  if (mode == 2) return dispatch_bn<DENSE_MN, DENSE_MN, true>(a, workspace_bytes, max_counters, 0, stream);
   return static_cast<int>(cudaErrorInvalidValue);
 }
 

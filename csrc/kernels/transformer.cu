@@ -258,6 +258,71 @@ __global__ void __launch_bounds__(256) xent_rows_kernel(const T* __restrict__ lo
   if (threadIdx.x == 0) row_loss[row] = mx + __logf(se) - zt;
 }
 
+// bf16 rows up to ~100 K columns: the row is read from global memory ONCE with 16-byte loads and kept in
+// shared memory for the max / sum / write passes (so dlogits may alias logits).  ld % 8 == 0.
+__global__ void __launch_bounds__(512) xent_rows_smem_kernel(const __nv_bfloat16* __restrict__ logits,
+                                                             const long long* __restrict__ target,
+                                                             __nv_bfloat16* __restrict__ dlogits,
+                                                             float* __restrict__ row_loss, int B, int V, int ld) {
+  extern __shared__ uint4 rowbuf[];
+  __shared__ float red[32];
+  const int row = blockIdx.x, nvec = ld >> 3;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const uint4* z = reinterpret_cast<const uint4*>(logits + (size_t)row * ld);
+  float mx = -FLT_MAX;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 v = z[i];
+    rowbuf[i] = v;
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      if (i * 8 + 2 * e < V) mx = fmaxf(mx, f.x);
+      if (i * 8 + 2 * e + 1 < V) mx = fmaxf(mx, f.y);
+    }
+  }
+  mx = warp_max(mx);
+  if (lane == 0) red[w] = mx;
+  __syncthreads();
+  mx = warp_max(lane < nw ? red[lane] : -FLT_MAX);
+  __syncthreads();
+  float se = 0.f;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 v = rowbuf[i];
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      if (i * 8 + 2 * e < V) se += __expf(f.x - mx);
+      if (i * 8 + 2 * e + 1 < V) se += __expf(f.y - mx);
+    }
+  }
+  se = warp_sum(se);
+  if (lane == 0) red[w] = se;
+  __syncthreads();
+  se = warp_sum(lane < nw ? red[lane] : 0.f);
+  const int t = (int)target[row];
+  const float zt = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(rowbuf)[t]);
+  const float inv = 1.f / se, inv_b = 1.f / (float)B;
+  uint4* d = reinterpret_cast<uint4*>(dlogits + (size_t)row * ld);
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 v = rowbuf[i];
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      const int c = i * 8 + 2 * e;
+      const float g0 = c < V ? (__expf(f.x - mx) * inv - (c == t ? 1.f : 0.f)) * inv_b : 0.f;
+      const float g1 = c + 1 < V ? (__expf(f.y - mx) * inv - (c + 1 == t ? 1.f : 0.f)) * inv_b : 0.f;
+      const __nv_bfloat162 r = __floats2bfloat162_rn(g0, g1);
+      o[e] = *reinterpret_cast<const uint32_t*>(&r);
+    }
+    d[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  if (threadIdx.x == 0) row_loss[row] = mx + __logf(se) - zt;
+}
+
 __global__ void __launch_bounds__(1024) mean_rows2_kernel(const float* __restrict__ row_loss, float* __restrict__ loss,
                                                           int B) {
   __shared__ float sh[32];
@@ -361,6 +426,18 @@ B200_API int b200_embedding_bwd(const long long* idx, const void* dout, float* d
 // `ld` = row pitch of logits / dlogits in elements (>= V; lets the LM head pad the vocabulary).
 B200_API int b200_xent_rows(const void* logits, const long long* target, void* dlogits, float* row_loss, float* loss,
                             int B, int V, int ld, int is_bf16, cudaStream_t st) {
+  const size_t row_bytes = (size_t)ld * 2;
+  if (is_bf16 && ld % 8 == 0 && row_bytes <= 200 * 1024 && ((uintptr_t)logits % 16 == 0) && ((uintptr_t)dlogits % 16 == 0)) {
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(xent_rows_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      configured = true;
+    }
+    xent_rows_smem_kernel<<<B, 512, row_bytes, st>>>((const bf16*)logits, target, (bf16*)dlogits, row_loss, B, V, ld);
+    mean_rows2_kernel<<<1, 1024, 0, st>>>(row_loss, loss, B);
+    B200_LAUNCH_CHECK();
+  }
   B200_DISPATCH(is_bf16,
                 (xent_rows_kernel<float><<<B, 256, 0, st>>>((const float*)logits, target, (float*)dlogits, row_loss, B, V, ld)),
                 (xent_rows_kernel<bf16><<<B, 256, 0, st>>>((const bf16*)logits, target, (bf16*)dlogits, row_loss, B, V, ld)));

@@ -82,14 +82,16 @@ class Block(nn.Module):
         return o.transpose(1, 2).reshape(b, t, d)
 
     def forward(self, x):
-        x = x + self.c_proj(self.attention(self.c_attn(self.ln_1(x))))
-        h = self.c_fc(self.ln_2(x))
-        if _native(h):
+        if _native(x) and self.c_fc.bias is not None:
             from ..ops import native_tf
 
-            h = native_tf.gelu(h)
-        else:
-            h = F.gelu(h, approximate="tanh")
+            # residual adds, GELU and its derivative ride in GEMM epilogues
+            a = self.attention(self.c_attn(self.ln_1(x)))
+            x = native_tf.linear_tc(a, self.c_proj.weight, self.c_proj.bias, residual=x)
+            return native_tf.mlp(self.ln_2(x), self.c_fc.weight, self.c_fc.bias, self.c_proj2.weight,
+                                 self.c_proj2.bias, residual=x)
+        x = x + self.c_proj(self.attention(self.c_attn(self.ln_1(x))))
+        h = F.gelu(self.c_fc(self.ln_2(x)), approximate="tanh")
         return x + self.c_proj2(h)
 
 

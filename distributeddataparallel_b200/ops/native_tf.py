@@ -40,16 +40,69 @@ def gemm_ex(a, b, out, mode: int, m: int, n: int, k: int, lda: int, ldb: int, ld
 
 
 # ---------------------------------------------------------------------------------------------
+_FUSED_EPILOGUES = os.environ.get("B200DDP_FUSED_EPILOGUES", "1") != "0"
+
+
+def set_fused_epilogues(enabled: bool) -> None:
+    global _FUSED_EPILOGUES
+    _FUSED_EPILOGUES = bool(enabled)
+
+
+def gemm_epi(a, b, out, mode: int, m: int, n: int, k: int, lda: int, ldb: int, ldo: int, epi: int,
+             bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None,
+             aux_out: Optional[torch.Tensor] = None) -> bool:
+    """GEMM with a fused epilogue on the persistent 2-CTA kernel (``b200_gemm_tc_epi``): epi 1 GELU forward
+    (``aux_out`` <- pre-activation), 2 GELU backward (times gelu'(``aux``)), 3 residual add (+ ``aux``).
+    Returns False when the shape is not eligible (nothing was launched)."""
+    if not _FUSED_EPILOGUES or a.dtype != torch.bfloat16 or out.dtype != torch.bfloat16:
+        return False
+    flags = 1 | 2 | ((_bf(bias) if bias is not None else 0) << 2)
+    desc = _ll11(lda, ldb, ldo, 1, 1, 0, 0, 0, 0, 0, 0)
+    s = scratch(a.device)
+    return _try_call("b200_gemm_tc_epi", _ptr(a), _ptr(b), _ptr(out), _ptr(bias), _ptr(aux), _ptr(aux_out), _i(epi),
+                     _i(m), _i(n), _i(k), _i(mode), _i(flags), desc, *_ws_args(a.device), _ptr(s.error), _stream()) == 0
+
+
+def _bias_grad(dy2, param, slot):
+    m, n = dy2.shape
+    db, _ = _grad_target(param, slot, param)
+    if _bf(dy2) and m >= 1024 and n % 2 == 0:
+        acc = torch.zeros(n, dtype=torch.float32, device=dy2.device)
+        _call("b200_colsum_bf16_acc", _ptr(dy2), _ptr(acc), _i(m), _i(n), _stream())
+        _call("b200_cast_from_f32", _ptr(acc), _ptr(db), _sz(n), _i(0), _i(1), _stream())
+    elif _bf(dy2):
+        _call("b200_colsum_bf16", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
+    else:
+        _call("b200_colsum", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
+    return db
+
+
+def _weight_grad(dy2, x2, w, param, slot):
+    (m, k), n = x2.shape, w.shape[0]
+    dw, _ = _grad_target(param, slot, w)
+    gemm_ex(dy2, x2, dw, 2, n, k, m, n, k, k)                           # dW = dy^T @ x
+    return dw
+
+
 class _LinearTC(torch.autograd.Function):
+    """y = x W^T + b (+ residual): the residual add rides in the GEMM epilogue when the shape allows."""
+
     @staticmethod
-    def forward(ctx, x, w, b):
+    def forward(ctx, x, w, b, residual=None):
         x2 = x.reshape(-1, x.shape[-1])
         if not x2.is_contiguous():
             x2 = x2.contiguous()
         m, k = x2.shape
         n = w.shape[0]
         y = torch.empty((m, n), dtype=x.dtype, device=x.device)
-        gemm_ex(x2, w, y, 0, m, n, k, k, k, n, bias=b)
+        fused = False
+        if residual is not None:
+            r2 = residual.reshape(m, n)
+            fused = r2.is_contiguous() and gemm_epi(x2, w, y, 0, m, n, k, k, k, n, 3, bias=b, aux=r2)
+        if not fused:
+            gemm_ex(x2, w, y, 0, m, n, k, k, k, n, bias=b)
+            if residual is not None:
+                y = y + residual.reshape(m, n)
         ctx.save_for_backward(x2, w)
         ctx.lead = x.shape[:-1]
         ctx.params = (w, b)
@@ -64,29 +117,74 @@ class _LinearTC(torch.autograd.Function):
         dy2 = dy.reshape(m, n)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        dx = dw = db = None
+        dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((m, k), dtype=x2.dtype, device=dy.device)
             gemm_ex(dy2, w, dx, 1, m, k, n, n, k, k)                    # dx = dy @ W
             dx = dx.reshape(*ctx.lead, k)
         if ctx.needs_input_grad[1]:
-            dw, _ = _grad_target(ctx.params[0], ctx.slots[0], w)
-            gemm_ex(dy2, x2, dw, 2, n, k, m, n, k, k)                   # dW = dy^T @ x
+            dw = _weight_grad(dy2, x2, w, ctx.params[0], ctx.slots[0])
         if ctx.params[1] is not None and ctx.needs_input_grad[2]:
-            db, _ = _grad_target(ctx.params[1], ctx.slots[1], ctx.params[1])
-            if _bf(dy2) and m >= 1024 and n % 2 == 0:
-                acc = torch.zeros(n, dtype=torch.float32, device=dy.device)
-                _call("b200_colsum_bf16_acc", _ptr(dy2), _ptr(acc), _i(m), _i(n), _stream())
-                _call("b200_cast_from_f32", _ptr(acc), _ptr(db), _sz(n), _i(0), _i(1), _stream())
-            elif _bf(dy2):
-                _call("b200_colsum_bf16", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
-            else:
-                _call("b200_colsum", _ptr(dy2), _ptr(db), _i(m), _i(n), _i(0), _stream())
-        return dx, dw, db
+            db = _bias_grad(dy2, ctx.params[1], ctx.slots[1])
+        if len(ctx.needs_input_grad) > 3 and ctx.needs_input_grad[3]:
+            dres = dy
+        return dx, dw, db, dres
 
 
-def linear_tc(x, w, b=None):
-    return _LinearTC.apply(x, w, b)
+def linear_tc(x, w, b=None, residual=None):
+    return _LinearTC.apply(x, w, b, residual)
+
+
+class _MLP(torch.autograd.Function):
+    """y = residual + gelu(x W1^T + b1) W2^T + b2 with GELU, its derivative and the residual add fused into
+    the epilogues of the three GEMMs they follow (transformer block feed-forward)."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual):
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        m, d = x2.shape
+        f = w1.shape[0]
+        pre = torch.empty((m, f), dtype=x.dtype, device=x.device)
+        act = torch.empty_like(pre)
+        if not gemm_epi(x2, w1, act, 0, m, f, d, d, d, f, 1, bias=b1, aux_out=pre):
+            gemm_ex(x2, w1, pre, 0, m, f, d, d, d, f, bias=b1)
+            _call("b200_gelu_fwd", _ptr(pre), _ptr(act), _sz(pre.numel()), _i(_bf(pre)), _stream())
+        y = torch.empty((m, d), dtype=x.dtype, device=x.device)
+        r2 = residual.reshape(m, d)
+        if not (r2.is_contiguous() and gemm_epi(act, w2, y, 0, m, d, f, f, f, d, 3, bias=b2, aux=r2)):
+            gemm_ex(act, w2, y, 0, m, d, f, f, f, d, bias=b2)
+            y = y + r2
+        ctx.save_for_backward(x2, pre, act, w1, w2)
+        ctx.shape = x.shape
+        ctx.params = (w1, b1, w2, b2)
+        ctx.slots = tuple(getattr(p, "_grad_slot", None) for p in ctx.params)
+        return y.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, pre, act, w1, w2 = ctx.saved_tensors
+        m, d = x2.shape
+        f = w1.shape[0]
+        dy2 = dy.reshape(m, d)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dpre = torch.empty_like(pre)
+        if not gemm_epi(dy2, w2, dpre, 1, m, f, d, d, f, f, 2, aux=pre):       # (dy W2) * gelu'(pre)
+            gemm_ex(dy2, w2, dpre, 1, m, f, d, d, f, f)
+            _call("b200_gelu_bwd", _ptr(pre), _ptr(dpre), _ptr(dpre), _sz(pre.numel()), _i(_bf(pre)), _stream())
+        dw2 = _weight_grad(dy2, act, w2, ctx.params[2], ctx.slots[2])
+        db2 = _bias_grad(dy2, ctx.params[3], ctx.slots[3])
+        dx = torch.empty((m, d), dtype=x2.dtype, device=dy.device)
+        gemm_ex(dpre, w1, dx, 1, m, d, f, f, d, d)
+        dw1 = _weight_grad(dpre, x2, w1, ctx.params[0], ctx.slots[0])
+        db1 = _bias_grad(dpre, ctx.params[1], ctx.slots[1])
+        return dx.reshape(ctx.shape), dw1, db1, dw2, db2, dy
+
+
+def mlp(x, w1, b1, w2, b2, residual):
+    return _MLP.apply(x, w1, b1, w2, b2, residual)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -314,12 +412,14 @@ class _LMHeadLoss(torch.autograd.Function):
     def backward(ctx, gout):
         x2, wte, dlogits = ctx.saved_tensors
         m, d, v, ld, xshape = ctx.cfg
-        _call("b200_scale_inplace", _ptr(dlogits), _sz(dlogits.numel()), _ptr(gout.contiguous().float()),
-              _i(_bf(dlogits)), _stream())
         dx = torch.empty((m, d), dtype=x2.dtype, device=x2.device)
         gemm_ex(dlogits, wte, dx, 1, m, d, v, ld, d, d)           # dx = dlogits @ wte
         dw = torch.empty_like(wte)                                # (tied with the embedding: autograd sums)
         gemm_ex(dlogits, x2, dw, 2, v, d, m, ld, d, d)            # dwte = dlogits^T @ x
+        # the incoming loss gradient scales the two (small) results instead of the [M, V] dlogits
+        g = gout.contiguous().float()
+        _call("b200_scale_inplace", _ptr(dx), _sz(dx.numel()), _ptr(g), _i(_bf(dx)), _stream())
+        _call("b200_scale_inplace", _ptr(dw), _sz(dw.numel()), _ptr(g), _i(_bf(dw)), _stream())
         return dx.reshape(xshape), dw, None
 
 

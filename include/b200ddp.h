@@ -115,6 +115,12 @@ int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float*
  * must be multiples of 4 (fp32) / 8 (bf16).  `error` (optional device word) is set if an
  * internal wait times out.  The conv entry points return cudaErrorNotSupported (801) for
  * shapes that need the FFMA fallback (channels not a multiple of 4). */
+/* b200_gemm_tc_ex with a fused epilogue on the persistent 2-CTA kernel (bf16 in/out): epi 1 = GELU forward
+ * (aux_out <- pre-activation, out <- gelu), 2 = GELU backward (out = result * gelu'(aux)), 3 = residual add
+ * (out = result + aux).  801 when the shape is not eligible: run the unfused kernels instead. */
+int b200_gemm_tc_epi(const void* A, const void* B, void* out, const void* bias, const void* aux, void* aux_out, int epi,
+                     int M, int N, int K, int mode, int flags, const long long* desc, float* workspace,
+                     size_t workspace_bytes, unsigned* counters, int max_counters, unsigned* error, cudaStream_t stream);
 int b200_gemm_tc(const void* A, const void* B, float* out, const float* bias, int M, int N, int K, int mode,
                  int bf16, int accumulate, float* workspace, size_t workspace_bytes, unsigned* counters,
                  int max_counters, unsigned* error, cudaStream_t stream);

@@ -95,3 +95,54 @@ def test_causal_attention_multi_tile_matches_sdpa(dtype, tol):
     out.backward(g.to("cuda", dtype))
     ref.backward(g)
     assert _rel(qkv.grad.cpu(), ref_in.grad) < 2 * tol, _rel(qkv.grad.cpu(), ref_in.grad)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m,dm", [(2048, 256), (4096, 1024)])
+def test_fused_mlp_epilogues_match_fp32_and_unfused(m, dm):
+    """GELU / GELU' / residual-add epilogues of the persistent GEMM vs the separate kernels and an fp32 reference."""
+    from distributeddataparallel_b200.ops import native, native_tf
+
+    torch.manual_seed(11)
+    f = 4 * dm
+    mk = lambda *s, sc=1.0: (torch.randn(*s, device="cuda") * sc).to(torch.bfloat16)
+    x, res, dy = mk(m, dm), mk(m, dm), mk(m, dm)
+    w1, b1, w2, b2 = mk(f, dm, sc=dm ** -0.5), mk(f, sc=0.1), mk(dm, f, sc=f ** -0.5), mk(dm, sc=0.1)
+    outs = {}
+    try:
+        for fused in (True, False):
+            native_tf.set_fused_epilogues(fused)
+            leaves = [t.clone().requires_grad_(True) for t in (x, w1, b1, w2, b2, res)]
+            y = native_tf.mlp(*leaves)
+            y.backward(dy)
+            outs[fused] = [y.detach()] + [t.grad for t in leaves]
+    finally:
+        native_tf.set_fused_epilogues(True)
+    torch.cuda.synchronize()
+    assert native.tc_error_word() == 0
+    leaves = [t.float().requires_grad_(True) for t in (x, w1, b1, w2, b2, res)]
+    xr, w1r, b1r, w2r, b2r, rr = leaves
+    yr = rr + torch.nn.functional.gelu(xr @ w1r.t() + b1r, approximate="tanh") @ w2r.t() + b2r
+    yr.backward(dy.float())
+    ref = [yr.detach()] + [t.grad for t in leaves]
+    names = ["y", "dx", "dw1", "db1", "dw2", "db2", "dres"]
+    for name, a, b_, r in zip(names, outs[True], outs[False], ref):
+        assert _rel(a, r) < 2e-2, (name, "fused vs fp32", _rel(a, r))
+        assert _rel(b_, r) < 2e-2, (name, "unfused vs fp32", _rel(b_, r))
+
+
+@pytest.mark.gpu
+def test_linear_residual_epilogue():
+    from distributeddataparallel_b200.ops import native_tf
+
+    torch.manual_seed(12)
+    m, k, n = 4096, 512, 1024
+    x = torch.randn(m, k, device="cuda").to(torch.bfloat16)
+    w = (torch.randn(n, k, device="cuda") * k ** -0.5).to(torch.bfloat16)
+    b = torch.randn(n, device="cuda").to(torch.bfloat16)
+    r = torch.randn(m, n, device="cuda").to(torch.bfloat16).requires_grad_(True)
+    y = native_tf.linear_tc(x, w, b, residual=r)
+    y.backward(torch.ones_like(y))
+    ref = x.float() @ w.float().t() + b.float() + r.detach().float()
+    assert _rel(y, ref) < 1e-2
+    assert torch.equal(r.grad, torch.ones_like(r))
