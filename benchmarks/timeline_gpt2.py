@@ -31,6 +31,14 @@ for e in prof.events():
         continue
     a = agg.setdefault(e.name[:95], [0, 0.0])
     a[0] += 1; a[1] += e.device_time
+if os.environ.get("B200DDP_SEQ_OUT"):
+    # every kernel of the LAST profiled step, in launch order, with its duration
+    evs = sorted((e for e in prof.events() if e.device_type.name == "CUDA"), key=lambda e: e.time_range.start)
+    evs = evs[len(evs) // 2:]
+    with open(os.environ["B200DDP_SEQ_OUT"], "w") as f:
+        t0 = evs[0].time_range.start
+        for e in evs:
+            f.write(f"{e.time_range.start - t0:10.1f} {e.device_time:8.1f} {e.name[:110]}\n")
 tot = sum(v[1] for v in agg.values())
 print(f"kernel time per step {tot/2/1e3:.2f} ms")
 for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:24]:

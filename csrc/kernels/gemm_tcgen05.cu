@@ -168,6 +168,15 @@ __device__ __forceinline__ void load_bf16x16(const __nv_bfloat16* p, float (&v)[
     v[2 * j] = x.x; v[2 * j + 1] = x.y; v[8 + 2 * j] = y.x; v[8 + 2 * j + 1] = y.y;
   }
 }
+__device__ __forceinline__ void unpack_bf16x16(const uint4& lo, const uint4& hi, float (&v)[16]) {
+  const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&lo);
+  const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&hi);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 x = __bfloat1622float2(a[j]), y = __bfloat1622float2(b[j]);
+    v[2 * j] = x.x; v[2 * j + 1] = x.y; v[8 + 2 * j] = y.x; v[8 + 2 * j + 1] = y.y;
+  }
+}
 __device__ __forceinline__ void store_bf16x16(__nv_bfloat16* p, const float (&v)[16]) {
   uint32_t w[8];
 #pragma unroll
@@ -738,6 +747,7 @@ __global__ void __launch_bounds__(256) peer_reduce_wait_kernel(PeerReduce pr, in
 // the epilogue for its own 128 rows out of its own TMEM.  TMA-only (dense operands), no split-K.
 // =====================================================================================================
 constexpr int T2_THREADS = 256;      // warp 0: TMA, warp 1: MMA (leader), warp 2: TMEM alloc, warps 4-7: epilogue
+constexpr int T2P_THREADS = 384;     // persistent variant: warps 4-11 are the epilogue (two per TMEM lane quarter)
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -908,7 +918,7 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
 }
 
 template <int AK, int BK_, int BN, bool BF16, int ST>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2P_THREADS, 1)
 gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
               int tiles_n, int num_tiles) {
   constexpr int ES = BF16 ? 2 : 4;
@@ -934,7 +944,7 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
-      mbar_init(&tmem_empty[b], 8);                          // 4 epilogue warps in each of the 2 CTAs
+      mbar_init(&tmem_empty[b], 16);                         // 8 epilogue warps in each of the 2 CTAs
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -993,21 +1003,36 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
       umma_commit2(&tmem_full[buf]);
     }
   } else if (warp >= 4) {
-    // ---- epilogue: TMEM -> registers -> global, 16 columns at a time ----
-    const int lane_grp = warp & 3;
+    // ---- epilogue: TMEM -> registers -> global, 16 columns at a time.  8 warps: warp w reads TMEM lane
+    // quarter w % 4 (hardware restriction) and the column half (w - 4) / 4 of the tile. ----
+    constexpr int NCH = BN / 32;                              // 16-column chunks per warp
+    const int lane_grp = warp & 3, half = (warp - 4) >> 2;
     const int row = lane_grp * 32 + lane;
     const uint32_t empty_leader0 = map_to_cta(smem_u32(&tmem_empty[0]), 0);
     const uint32_t empty_leader1 = map_to_cta(smem_u32(&tmem_empty[1]), 0);
     int it = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
       const int buf = it & 1;
-      const int m0 = (tile / tiles_n) * 2 * BM + (int)cta * BM, n0 = (tile % tiles_n) * BN;
+      const int m0 = (tile / tiles_n) * 2 * BM + (int)cta * BM, n0 = (tile % tiles_n) * BN + half * (BN / 2);
+      const int gr = m0 + row;
+      // operands of the fused epilogue do not depend on the accumulator: fetch them while the MMAs run
+      uint4 ax[2 * NCH];
+      if (a.epi >= 2) {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          const int gc0 = n0 + c * 16;
+          if (gr < a.M && gc0 < a.N) {
+            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(a.aux) + (size_t)gr * a.ldo + gc0);
+            ax[2 * c] = src[0];
+            ax[2 * c + 1] = src[1];
+          }
+        }
+      }
       mbar_wait(&tmem_full[buf], (it >> 1) & 1, a.error);
       tc_fence_after();
-      const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(buf * BN);
-      const int gr = m0 + row;
-#pragma unroll 1
-      for (int c = 0; c < BN / 16; ++c) {
+      const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)(buf * BN + half * (BN / 2));
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
         float acc[16];
         tmem_ld16(tmem_row + c * 16, acc);
         const int gc0 = n0 + c * 16;
@@ -1026,7 +1051,7 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
             for (int j = 0; j < 16; ++j) acc[j] = gelu_tanh(acc[j]);
           } else {
             float x[16];
-            load_bf16x16(reinterpret_cast<const __nv_bfloat16*>(a.aux) + o, x);
+            unpack_bf16x16(ax[2 * c], ax[2 * c + 1], x);
 #pragma unroll
             for (int j = 0; j < 16; ++j) acc[j] = a.epi == 2 ? acc[j] * gelu_tanh_grad(x[j]) : acc[j] + x[j];
           }
@@ -1127,7 +1152,7 @@ static int launch2(const Args& a_in, cudaStream_t st) {
     }
     const int tiles_n = ceil_div(a.N, BN), num_tiles = ceil_div(a.M, 2 * BM) * tiles_n;
     const int clusters = min(num_tiles, kNumSMs / 2);
-    kp<<<dim3(2 * clusters), T2_THREADS, smem, st>>>(a, map_a, map_b, tiles_n, num_tiles);
+    kp<<<dim3(2 * clusters), T2P_THREADS, smem, st>>>(a, map_a, map_b, tiles_n, num_tiles);
     return static_cast<int>(cudaPeekAtLastError());
   }
   dim3 grid(2 * ceil_div(a.M, 2 * BM), ceil_div(a.N, BN));
@@ -1147,7 +1172,8 @@ static int try_2cta(const Args& a, cudaStream_t st) {
     // ties go to the wider tile (half the A traffic per flop)
     const long long rows = ceil_div(a.M, 2 * BM), t256 = rows * ceil_div(a.N, 256), t128 = rows * ceil_div(a.N, 128);
     const long long clusters = kNumSMs / 2;
-    const long long c256 = ((t256 + clusters - 1) / clusters) * 256, c128 = ((t128 + clusters - 1) / clusters) * 128;
+    // (a 128-wide tile costs ~0.8 of a 256-wide one: twice the A traffic per flop runs into L2 bandwidth)
+    const long long c256 = ((t256 + clusters - 1) / clusters) * 256, c128 = ((t128 + clusters - 1) / clusters) * 200;
     const int bn = (a.N >= 256 && c256 <= c128) ? 256 : 128;
     if ((bn == 256 ? t256 : t128) < 24) return -1;           // too few cluster tiles: keep 1-CTA + split-K
     if (bn == 256) return launch2<AK, BK_, 256, BF16>(a, st);
