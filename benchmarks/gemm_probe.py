@@ -58,6 +58,7 @@ def main():
     ap.add_argument("--one", default=None)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--epilogues", action="store_true", help="also time bias / residual / GELU epilogue variants")
     args = ap.parse_args()
     shapes = SHAPES
     if args.one:
@@ -79,6 +80,19 @@ def main():
             err = (out[0].float() - ref(A[0], B[0], mode).float()).abs().max().item()
             line += f" | cuBLAS {t_ref:8.1f} us {flops / t_ref / 1e6:7.1f} TF | ratio {t_ref / t_ours:5.2f} maxerr {err:.3g}"
         print(line, flush=True)
+        if args.epilogues and mode != 2:
+            bias = torch.randn(n, device="cuda", dtype=torch.bfloat16)
+            aux = [torch.randn(m, n, device="cuda", dtype=torch.bfloat16) for _ in range(copies)]
+            t_b = time_fn(lambda i: native_tf.gemm_ex(A[i], B[i], out[i], mode, m, n, k, lda, ldb, n, bias=bias), copies, args.iters)
+            row = f"            +bias {t_b:7.1f} us"
+            for epi, nm in ((3, "+bias+residual"), (1, "+bias+gelu"), (2, "*gelu'(aux)")):
+                kw = dict(aux_out=aux[0]) if epi == 1 else dict(aux=aux[0])
+                if native_tf.gemm_epi(A[0], B[0], out[0], mode, m, n, k, lda, ldb, n, epi, bias=bias if epi != 2 else None, **kw):
+                    fn = lambda i: native_tf.gemm_epi(A[i], B[i], out[i], mode, m, n, k, lda, ldb, n, epi,
+                                                      bias=bias if epi != 2 else None,
+                                                      **(dict(aux_out=aux[i]) if epi == 1 else dict(aux=aux[i])))
+                    row += f" | {nm} {time_fn(fn, copies, args.iters):7.1f} us"
+            print(row, flush=True)
         del A, B, out
 
 

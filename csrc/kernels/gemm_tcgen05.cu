@@ -930,6 +930,7 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[ST], empty_bar[ST], tmem_full[2], tmem_empty[2];
   __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[2][BN];             // this tile's bias, staged once per tile by the epilogue warps
 
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   const uint32_t cta = cluster_ctarank();
@@ -1015,6 +1016,11 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
       const int buf = it & 1;
       const int m0 = (tile / tiles_n) * 2 * BM + (int)cta * BM, n0 = (tile % tiles_n) * BN + half * (BN / 2);
       const int gr = m0 + row;
+      if (a.bias != nullptr) {
+        const int nt0 = (tile % tiles_n) * BN;
+        for (int i = (warp - 4) * 32 + lane; i < BN; i += 256) bias_s[buf][i] = nt0 + i < a.N ? load_bias(a, nt0 + i) : 0.f;
+        asm volatile("bar.sync 1, 256;" ::: "memory");       // the 8 epilogue warps only
+      }
       // operands of the fused epilogue do not depend on the accumulator: fetch them while the MMAs run
       uint4 ax[2 * NCH];
       if (a.epi >= 2) {
@@ -1038,9 +1044,12 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
         const int gc0 = n0 + c * 16;
         if (gr >= a.M || gc0 >= a.N) continue;
         if (a.bias != nullptr) {
+          const float4* bs = reinterpret_cast<const float4*>(&bias_s[buf][half * (BN / 2) + c * 16]);
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (gc0 + j < a.N) acc[j] += load_bias(a, gc0 + j);
+          for (int j = 0; j < 4; ++j) {
+            const float4 b4 = bs[j];
+            acc[4 * j] += b4.x; acc[4 * j + 1] += b4.y; acc[4 * j + 2] += b4.z; acc[4 * j + 3] += b4.w;
+          }
         }
         const size_t o = (size_t)gr * a.ldo + gc0;
         const bool full = gc0 + 15 < a.N && !a.accumulate;
