@@ -45,5 +45,6 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("has_rebuilt", &Reducer::has_rebuilt)
       .def("note_graph_replay", &Reducer::note_graph_replay)
       .def("_autograd_hook", &Reducer::autograd_hook, release())
+      .def("shadow_backward", &Reducer::shadow_backward, release())
       .def("_finalize_backward", &Reducer::finalize_backward, release());
 }

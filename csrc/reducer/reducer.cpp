@@ -487,6 +487,36 @@ void Reducer::finalize_backward() {
   armed_ = false;
 }
 
+void Reducer::shadow_backward() {
+  {
+    std::unique_lock<std::mutex> lock(mu_);
+    TORCH_CHECK(!armed_ || next_bucket_ == 0 || next_bucket_ == num_buckets(),
+                "shadow_backward called while a reduction is in flight");
+    {
+      py::gil_scoped_acquire gil;
+      reset_round();
+    }
+    armed_ = true;
+    t_backward_start_ = clock::now();
+    {
+      at::NoGradGuard no_grad;
+      for (auto& b : buckets_) {
+        b.flat.zero_();
+        b.pending = 0;
+      }
+    }
+    std::fill(ready_.begin(), ready_.end(), 1);
+    if (!recorded_order_ && !has_rebuilt_) {
+      // no real backward ever ran on this rank: record the conventional reverse registration order
+      // (rank 0's order is the one every rank adopts at the rebuild)
+      ready_order_.clear();
+      for (int64_t i = static_cast<int64_t>(params_.size()) - 1; i >= 0; --i) ready_order_.push_back(i);
+    }
+    launch_ready_buckets();
+  }
+  finalize_backward();
+}
+
 bool Reducer::should_rebuild_buckets() const {
   std::lock_guard<std::mutex> lock(mu_);
   return !has_rebuilt_ && recorded_order_ && !find_unused_ &&

@@ -111,6 +111,9 @@ class Reducer {
   // test hooks
   void autograd_hook(int64_t index);
   void finalize_backward();
+  // Uneven inputs (DistributedDataParallel.join): a rank that has run out of data takes part in one
+  // iteration's bucket reductions with all-zero gradients, issuing exactly the launches an active rank issues.
+  void shadow_backward();
 
  private:
   void build_buckets(const std::vector<std::vector<int64_t>>& bucket_indices);

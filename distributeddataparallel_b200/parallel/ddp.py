@@ -95,7 +95,10 @@ class DistributedDataParallel(nn.Module):
         self.broadcast_bucket_size = 250 * MiB
         self.allreduce_algo = allreduce_algo
         self._comm_hook_name = "builtin"
-        self._collectives = {"broadcast": 0, "allgather": 0}
+        self._collectives = {"broadcast": 0, "allgather": 0, "allreduce_control": 0}
+        self._join_enabled = False
+        self._join_iterations = 0
+        self._buffer_src = 0               # rank whose buffers are broadcast before each forward
         self._rebuilt_bucket_sizes: List[int] = []
         self._graph_mode = False
 
@@ -191,11 +194,11 @@ class DistributedDataParallel(nn.Module):
             if msg:
                 raise RuntimeError(f"DDP expects the same model across all ranks, but rank {self.rank}: {msg}")
 
-    def _sync_module_states(self) -> None:
+    def _sync_module_states(self, src: int = 0) -> None:
         params = [p.detach() for p in self.module.parameters()]
         bufs = [b.detach() for b in self.module.buffers()]
         self._collectives["broadcast"] += broadcast_coalesced(
-            self._comm, params + bufs, self.broadcast_bucket_size, src=0)
+            self._comm, params + bufs, self.broadcast_bucket_size, src=src)
 
     def _publish_grad_slots(self) -> None:
         """Expose each parameter's bucket slot so in-place wgrad kernels can target it."""
@@ -205,6 +208,9 @@ class DistributedDataParallel(nn.Module):
 
     # -- forward ---------------------------------------------------------------------------
     def _pre_forward(self) -> None:
+        if self._join_enabled and torch.is_grad_enabled() and self.require_backward_grad_sync:
+            self._join_poll(1)              # tell ranks that already ran out of data to shadow this iteration
+            self._join_iterations += 1
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self.reducer.prepare_for_forward()
             if self.reducer.should_rebuild_buckets():
@@ -229,11 +235,11 @@ class DistributedDataParallel(nn.Module):
     def _sync_buffers(self) -> None:
         with torch.no_grad():
             sync = getattr(self._comm, "sync_buffers", None)
-            if sync is not None:
+            if sync is not None and self._buffer_src == 0:
                 self._collectives["broadcast"] += sync(self.module, self._buffers_for_sync)
             else:
                 self._collectives["broadcast"] += broadcast_coalesced(
-                    self._comm, self._buffers_for_sync, self.broadcast_bucket_size, src=0)
+                    self._comm, self._buffers_for_sync, self.broadcast_bucket_size, src=self._buffer_src)
 
     def forward(self, *inputs, **kwargs):
         with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
@@ -257,6 +263,61 @@ class DistributedDataParallel(nn.Module):
         finally:
             self.require_backward_grad_sync = old
             self.reducer.set_require_sync(old)
+
+    # -- uneven inputs ----------------------------------------------------------------------
+    def _control_tensor(self, values) -> torch.Tensor:
+        dev = self.device if dist.get_backend(self.process_group) == "nccl" else torch.device("cpu")
+        return torch.tensor(values, dtype=torch.int64, device=dev)
+
+    def _join_poll(self, active: int) -> int:
+        """One tiny all-reduce per iteration while ``join()`` is active.  Returns the highest rank that still
+        has data (-1: none) -- that rank is the source of this iteration's buffer broadcast, as in stock DDP."""
+        t = self._control_tensor([self.rank if active else -1])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.process_group)
+        self._collectives["allreduce_control"] += 1
+        self._buffer_src = max(int(t.item()), 0)
+        return int(t.item())
+
+    def _shadow_iteration(self) -> None:
+        """What a rank without data does while others train: the same collectives, zero gradients."""
+        self.reducer.prepare_for_forward()
+        if self.reducer.should_rebuild_buckets():
+            self._rebuild_buckets()
+        if self.broadcast_buffers and self._buffers_for_sync:
+            self._sync_buffers()
+        self.reducer.shadow_backward()
+
+    @contextlib.contextmanager
+    def join(self, divide_by_initial_world_size: bool = True, enable: bool = True,
+             throw_on_early_termination: bool = False):
+        """Train with a different number of batches per rank (``DistributedDataParallel.join``,
+        distributed.py:1798).  A rank that leaves the context first keeps matching the other ranks'
+        collectives with zero gradients (still divided by the full world size); when the last rank
+        leaves, its parameters and buffers are broadcast so every replica ends identical."""
+        if not enable or self.world_size == 1:
+            yield
+            return
+        if not divide_by_initial_world_size:
+            raise NotImplementedError("join(divide_by_initial_world_size=False): the 1/world_size factor is fused "
+                                      "into the reduction kernels; only the default is supported")
+        if throw_on_early_termination:
+            raise NotImplementedError("join(throw_on_early_termination=True) is not supported")
+        self._join_enabled = True
+        self._join_iterations = 0
+        try:
+            yield
+        except BaseException:
+            self._join_enabled = False
+            raise
+        while self._join_poll(0) >= 0:
+            self._shadow_iteration()
+        self._join_enabled = False
+        self._buffer_src = 0
+        # the replica that trained longest (highest rank among ties) is authoritative
+        key = self._control_tensor([self._join_iterations * self.world_size + self.rank])
+        dist.all_reduce(key, op=dist.ReduceOp.MAX, group=self.process_group)
+        self._collectives["allreduce_control"] += 1
+        self._sync_module_states(src=int(key.item()) % self.world_size)
 
     def register_comm_hook(self, state, hook: Callable) -> None:
         """``hook(state, bucket: GradBucket) -> Future[Tensor]``; the hook owns the averaging."""

@@ -170,3 +170,38 @@ def failing_worker(rank, ws, port):
         raise ValueError("injected failure on rank 1")
     dist.barrier()          # rank 0 blocks here until torn down by the launcher
     d.cleanup()
+
+
+def join_worker(rank, ws, port, out_dir):
+    """Uneven inputs: rank r trains 2 + 3*r iterations inside join(); ours vs stock DDP's join()."""
+    d = _init(rank, ws, port)
+    from torch.nn.parallel import DistributedDataParallel as StockDDP
+
+    d.ops.set_native(False)
+    torch.manual_seed(5)
+    a, b = TinyNet(), TinyNet()
+    b.load_state_dict(a.state_dict())
+    mine = d.DDP(a, comm="c10d", bucket_cap_mb=0.0005)       # several buckets + a rebuild inside the join
+    stock = StockDDP(b, bucket_cap_mb=0.0005)
+    opt_a = torch.optim.SGD(mine.parameters(), lr=0.05)
+    opt_b = torch.optim.SGD(stock.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(11 + rank)
+    batches = [(torch.randn(6, 8, generator=g), torch.randn(6, 4, generator=g)) for _ in range(2 + 3 * rank)]
+    for model, opt in ((mine, opt_a), (stock, opt_b)):
+        with model.join():
+            for x, y in batches:
+                opt.zero_grad()
+                loss = ((model(x)[:, :4] - y) ** 2).mean() + 0.0 * sum(p.sum() for p in model.module.unused.parameters())
+                loss.backward()
+                opt.step()
+    pa = torch.cat([p.detach().reshape(-1) for p in mine.parameters()] + [t.detach().float().reshape(-1) for t in mine.buffers()])
+    pb = torch.cat([p.detach().reshape(-1) for p in stock.parameters()] + [t.detach().float().reshape(-1) for t in stock.buffers()])
+    gathered = [torch.zeros_like(pa) for _ in range(ws)]
+    dist.all_gather(gathered, pa)
+    rec = {"identical_across_ranks": all(torch.equal(gathered[0], t) for t in gathered),
+           "err_vs_stock": float((pa - pb).norm() / pb.norm()),
+           "param_err": float(max((x.detach() - y.detach()).abs().max() for x, y in zip(mine.parameters(), stock.parameters()))),
+           "control": mine._get_ddp_logging_data()["collectives"]["allreduce_control"],
+           "iters": len(batches)}
+    torch.save(rec, os.path.join(out_dir, f"join{rank}.pt"))
+    d.cleanup()

@@ -71,6 +71,18 @@ def test_train_and_resume(tmp_path):
     assert s1["steps"] >= 7
 
 
+def test_join_uneven_inputs_matches_stock(tmp_path):
+    """DDP.join(): rank 0 runs 2 iterations, rank 1 runs 5; nobody hangs, replicas end identical and equal
+    to what stock DDP's join() produces on the same data."""
+    ws = 2
+    mp.spawn(W.join_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    for r in range(ws):
+        rec = torch.load(tmp_path / f"join{r}.pt")
+        assert rec["identical_across_ranks"]
+        assert rec["err_vs_stock"] < 1e-5, rec
+        assert rec["control"] >= rec["iters"] + 1
+
+
 def test_fault_injection_fail_fast():
     ws = 2
     with pytest.raises(Exception) as ei:
