@@ -268,10 +268,26 @@ def _conv_geom(x: torch.Tensor, w: torch.Tensor, stride: int, pad: int):
     return n, h, wd, c, k, r, s, p, q
 
 
+def _pad_channels(t: torch.Tensor, c_to: int) -> torch.Tensor:
+    """[N, C, H, W] channels-last -> [N, c_to, H, W] channels-last with zero-filled extra channels."""
+    n, c, h, w = t.shape
+    out = t.new_zeros((n, h, w, c_to))
+    out[..., :c] = t.permute(0, 2, 3, 1)
+    return out.permute(0, 3, 1, 2)
+
+
 class _Conv2d(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, stride, pad, stats):
         xc, wc = _nhwc(x), _nhwc(w)
+        c_real = xc.shape[1]
+        # An RGB stem (C = 3) has no 16-byte channel vectors, which both the tcgen05 gathers and the vectorised
+        # FFMA loads need: run it as a 4-channel convolution with a zero fourth channel (its filter gradient
+        # is exactly zero and is dropped again in backward).
+        padded = c_real % 4 != 0 and _tc_mode != "0" and not ctx.needs_input_grad[0]
+        if padded:
+            c4 = (c_real + 3) // 4 * 4
+            xc, wc = _pad_channels(xc, c4), _pad_channels(wc, c4)
         n, h, wd, c, k, r, s, p, q = _conv_geom(xc, wc, stride, pad)
         y = _empty_nhwc(n, k, p, q, x.device)
         _conv_call("b200_conv2d_fprop", (_ptr(xc), _ptr(wc), _ptr(y), _ptr(stats)),
@@ -280,6 +296,7 @@ class _Conv2d(torch.autograd.Function):
         ctx.geom = (n, h, wd, c, k, r, s, stride, pad)
         ctx.param = w
         ctx.slot = getattr(w, "_grad_slot", None)
+        ctx.c_real = c_real if padded else None
         return y
 
     @staticmethod
@@ -293,8 +310,17 @@ class _Conv2d(torch.autograd.Function):
             dx = _empty_nhwc(n, c, h, wd, dy.device)
             _conv_call("b200_conv2d_dgrad", (_ptr(dy), _ptr(wc), _ptr(dx)), geom, dy.device)
         if ctx.needs_input_grad[1]:
-            dw, acc = _grad_target(ctx.param, ctx.slot, wc)
-            _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device)
+            if ctx.c_real is None:
+                dw, acc = _grad_target(ctx.param, ctx.slot, wc)
+                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device)
+            else:
+                dw_pad = torch.empty_like(wc)
+                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw_pad), _i(0)), geom, dy.device)
+                dw, acc = _grad_target(ctx.param, ctx.slot, _nhwc(ctx.param))
+                if acc:
+                    dw.add_(dw_pad[:, :ctx.c_real])
+                else:
+                    dw.copy_(dw_pad[:, :ctx.c_real])
         return dx, dw, None, None, None
 
 

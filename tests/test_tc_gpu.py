@@ -87,11 +87,24 @@ def test_conv_tc_matches_fp64(nat, shape):
     assert nat.tc_error_word() == 0
 
 
-def test_stem_falls_back_to_ffma(nat):
+def test_rgb_stem_runs_on_tensor_cores_with_a_zero_fourth_channel(nat):
+    """C = 3 has no 16-byte channel vectors: the stem is run as a 4-channel convolution (zero channel added)
+    when its input needs no gradient; with an input gradient requested it stays on the FFMA kernels."""
     nat.set_tensor_cores(True)
-    before = nat.ffma_launches
-    x = _cl(torch.randn(4, 3, 32, 32, device="cuda"))
-    w = _cl(torch.randn(64, 3, 7, 7, device="cuda"))
+    x = _cl(torch.randn(8, 3, 32, 32, device="cuda"))
+    w = _cl(torch.randn(64, 3, 7, 7, device="cuda")).requires_grad_(True)
+    tc0, ff0 = nat.tc_launches, nat.ffma_launches
     y = nat.conv2d(x, w, 2, 3)
-    assert nat.ffma_launches == before + 1
-    assert _rel(y, F.conv2d(x.double(), w.double(), None, 2, 3)) < 1e-5
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    assert nat.tc_launches == tc0 + 2 and nat.ffma_launches == ff0          # fprop + wgrad on tcgen05
+    xd, wd = x.double(), w.detach().double().requires_grad_(True)
+    yd = F.conv2d(xd, wd, None, 2, 3)
+    yd.backward(dy.double())
+    assert _rel(y, yd) < 2e-3 and _rel(w.grad, wd.grad) < 2e-3
+    assert w.grad.shape == w.shape
+    xg = x.clone().requires_grad_(True)
+    ff1 = nat.ffma_launches
+    y2 = nat.conv2d(xg, w, 2, 3)
+    assert nat.ffma_launches == ff1 + 1
+    assert _rel(y2, yd) < 1e-5
