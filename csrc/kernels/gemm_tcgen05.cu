@@ -373,6 +373,22 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
     // TMA boxes: K-major operand = one box [ROWS x 128 B]; bf16 MN-major operand = ROWS/64 boxes of
     // [64 k rows x 128 B of mn], 8 KB each.  Both land in the SWIZZLE_128B layout the MMA expects.
     const uint32_t tx_bytes = (a.tma_a ? (uint32_t)A_STAGE : 0u) + (a.tma_b ? (uint32_t)B_STAGE : 0u);
+    // im2col-mode TMA: window corner (w, h, n) of the tile's first output pixel
+    int im_w_a = 0, im_h_a = 0, im_n_a = 0, im_w_b = 0, im_h_b = 0, im_n_b = 0;
+    if (t == 0 && a.tma_a == 2) {
+      int t1, q, p;
+      a.g.fQ.divmod(m0, t1, q);
+      a.g.fP.divmod(t1, im_n_a, p);
+      im_w_a = q * a.g.stride - a.g.pad;
+      im_h_a = p * a.g.stride - a.g.pad;
+    }
+    if (t == 0 && a.tma_b == 2) {
+      int t1, q, p;
+      a.g.fQ.divmod(n0, t1, q);
+      a.g.fP.divmod(t1, im_n_b, p);
+      im_w_b = q * a.g.stride - a.g.pad;
+      im_h_b = p * a.g.stride - a.g.pad;
+    }
     if (any_gather || t == 0) {
       int issued = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
@@ -381,12 +397,21 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         const int k0 = k_begin + kb * KELEMS;
         if (t == 0 && tx_bytes) {
           mbar_expect_tx(&full_bar[s], tx_bytes);
-          if (a.tma_a) {
+          if (a.tma_a == 2 || a.tma_b == 2) {              // k-block -> (filter tap, first channel)
+            int rs, c0, r, sx;
+            a.g.fC.divmod(k0, rs, c0);
+            a.g.fS.divmod(rs, r, sx);
+            if (a.tma_a == 2)
+              tma_load_im2col_4d(smem_a + s * A_STAGE, &map_a, c0, im_w_a, im_h_a, im_n_a, (unsigned short)sx, (unsigned short)r, &full_bar[s]);
+            if (a.tma_b == 2)
+              tma_load_im2col_4d(smem_b + s * B_STAGE, &map_b, c0, im_w_b, im_h_b, im_n_b, (unsigned short)sx, (unsigned short)r, &full_bar[s]);
+          }
+          if (a.tma_a == 1) {
             if (!is_mn(AK)) tma_load_2d(smem_a + s * A_STAGE, &map_a, k0, m0, &full_bar[s]);
             else
               for (int bx = 0; bx < BM / 64; ++bx) tma_load_2d(smem_a + s * A_STAGE + bx * 8192, &map_a, m0 + bx * 64, k0, &full_bar[s]);
           }
-          if (a.tma_b) {
+          if (a.tma_b == 1) {
             if (!is_mn(BK_)) tma_load_2d(smem_b + s * B_STAGE, &map_b, k0, n0, &full_bar[s]);
             else
               for (int bx = 0; bx < BN / 64; ++bx) tma_load_2d(smem_b + s * B_STAGE + bx * 8192, &map_b, n0 + bx * 64, k0, &full_bar[s]);
@@ -436,7 +461,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
       for (int j = 0; j < KELEMS / UMMA_K; ++j) {
         // a TMA-fetched bf16 MN-major operand sits in the SWIZZLE_128B MN-major layout instead:
         // 64-mn atoms 8 KB apart (LBO), 8-k-row atoms 1 KB apart (SBO), 2 k-atoms per MMA
-        const bool a_mn_tma = is_mn(AK) && a.tma_a, b_mn_tma = is_mn(BK_) && a.tma_b;
+        const bool a_mn_tma = is_mn(AK) && a.tma_a == 1, b_mn_tma = is_mn(BK_) && a.tma_b == 1;
         const uint64_t da = a_mn_tma ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
                                      : make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
         const uint64_t db = b_mn_tma ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
@@ -1089,6 +1114,25 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
   if (warp == 2) tmem_dealloc2(tmem_d, TMEM_COLS);
 }
 
+// wt[c][R-1-r][S-1-s][k] = w[k][r][s][c]: the filter of the convolution that computes dX from dY (stride 1).
+// One 32 x 32 (k, c) tile per block through shared memory, both sides coalesced.
+__global__ void __launch_bounds__(256) flip_transpose_filter_kernel(const float* __restrict__ w, float* __restrict__ wt, int K,
+                                                                    int C, int RS) {
+  __shared__ float tile[32][33];
+  const int rs = blockIdx.z, k0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int i = ty; i < 32; i += 8) {
+    const int k = k0 + i, c = c0 + tx;
+    if (k < K && c < C) tile[i][tx] = w[((size_t)k * RS + rs) * C + c];
+  }
+  __syncthreads();
+  const int rs_f = RS - 1 - rs;                 // (R-1-r) * S + (S-1-s)
+  for (int i = ty; i < 32; i += 8) {
+    const int c = c0 + i, k = k0 + tx;
+    if (k < K && c < C) wt[((size_t)c * RS + rs_f) * K + k] = tile[tx][i];
+  }
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 // 2-D row-major global matrix [outer x inner] with `pitch` elements per row; box [box_outer x box_inner];
 // 128-byte swizzle; out-of-range parts of a box are zero-filled.
@@ -1098,6 +1142,10 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inne
 }
 
 static bool g_use_tma = true;
+static bool g_use_im2col_tma = true;
+static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom& g, int channels, int pixels) {
+  return tma_make_map_im2col(m, x, bf16, g.Nb, g.H, g.W, g.C, g.R, g.S, g.P, g.Q, g.stride, g.pad, channels, pixels);
+}
 
 template <int AK, int BK_, int BN, bool BF16>
 static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
@@ -1112,6 +1160,11 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     else if (AK == DENSE_MN && BF16) a.tma_a = make_map(&map_a, a.a, true, a.M, a.Kd, a.lda, 64, KELEMS);
     if (BK_ == DENSE_K) a.tma_b = make_map(&map_b, a.b, BF16, a.Kd, a.N, a.ldb, KELEMS, BN);
     else if (BK_ == DENSE_MN && BF16 && BN >= 64) a.tma_b = make_map(&map_b, a.b, true, a.N, a.Kd, a.ldb, 64, KELEMS);
+    // convolution activations: im2col-mode TMA when a k-block never straddles a filter tap
+    if (g_use_im2col_tma && a.g.C % KELEMS == 0) {
+      if (AK == IM2COL_K && make_im2col_map(&map_a, a.a, BF16, a.g, KELEMS, BM)) a.tma_a = 2;
+      if (BK_ == IM2COL_K && make_im2col_map(&map_b, a.b, BF16, a.g, KELEMS, BN)) a.tma_b = 2;
+    }
   }
   static bool configured = false;     // per template instantiation
   if (!configured) {
@@ -1243,6 +1296,7 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 // 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_use_im2col_tma(int enabled) { b200::tc::g_use_im2col_tma = enabled != 0; }
 B200_API void b200_gemm_tc_use_2cta(int mode) { b200::tc::g_use_2cta = mode; }   // 0 off, 1 simple, 2 persistent
 
 // Dense (optionally batched) GEMM; inputs fp32 (TF32 math) or bf16, output fp32 or bf16:
@@ -1359,6 +1413,26 @@ B200_API int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, in
   const int pixels = Nb * H * W;
   a.Kd = R * S * K; a.workspace = workspace; a.counters = counters; a.error = error; a.out = dx; a.ldo = C;
   const bool pointwise = R == 1 && S == 1 && stride == 1 && pad == 0;   // dX = dY[pixels,K] * W[K,C]
+  // Stride-1 filters: dX is itself a convolution of dY (padding R-1-pad) with the flipped, transposed filter.
+  // The filter is re-laid-out into the tail of the workspace (a few MB at most), after which the forward kernels
+  // -- im2col-mode TMA for dY, tiled TMA for the filter -- do the work; no gather code runs on the SMs.
+  const size_t wt_bytes = (size_t)C * R * S * K * sizeof(float);
+  if (!pointwise && g_use_im2col_tma && g_use_tma && stride == 1 && R == S && R - 1 - pad >= 0 && K % 32 == 0 && workspace &&
+      2 * wt_bytes <= workspace_bytes) {
+    const size_t ws_left = (workspace_bytes - wt_bytes) & ~(size_t)255;
+    float* wt = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ws_left);
+    dim3 tg((C + 31) / 32, (K + 31) / 32, R * S);
+    flip_transpose_filter_kernel<<<tg, 256, 0, stream>>>(w, wt, K, C, R * S);
+    Args f{};
+    f.g = make_geom(Nb, a.g.P, a.g.Q, K, C, R, S, 1, R - 1 - pad);        // input = dY [N,P,Q,K], C output channels
+    f.Kd = R * S * K; f.workspace = workspace; f.counters = counters; f.error = error; f.out = dx; f.ldo = C;
+    if (pixels >= 1024 || C < 128) {
+      f.a = dy; f.b = wt; f.lda = K; f.ldb = f.Kd; f.M = pixels; f.N = C;
+      return dispatch_bn<IM2COL_K, DENSE_K, false>(f, ws_left, max_counters, 0, stream);
+    }
+    f.a = wt; f.b = dy; f.lda = f.Kd; f.ldb = K; f.M = C; f.N = pixels; f.transpose_out = 1;
+    return dispatch_bn<DENSE_K, IM2COL_K, false>(f, ws_left, max_counters, 0, stream);
+  }
   if (pixels >= 1024 || C < 128) {
     a.a = dy; a.b = w; a.lda = K; a.ldb = C; a.M = pixels; a.N = C;
     if (pointwise) return dispatch_bn<DENSE_K, DENSE_MN, false>(a, workspace_bytes, max_counters, 0, stream);

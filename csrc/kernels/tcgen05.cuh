@@ -74,6 +74,16 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 
+// 4-D im2col-mode TMA load (NHWC activations): box = pixels_per_column pixels x channels_per_pixel channels,
+// starting at base pixel (w, h, n) -- input-space coordinates of the filter window's corner, may be negative
+// inside the padding -- shifted by the filter tap (off_w, off_h); rows land like a tiled load (128 B, swizzled).
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorMap* map, int c, int w, int h, int n,
+                                                   unsigned short off_w, unsigned short off_h, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(dst), "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h) : "memory");
+}
+
 template <bool BF16>
 __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
   if (BF16) {
@@ -166,6 +176,54 @@ static inline bool tma_make_map_2d(CUtensorMap* m, const void* base, bool bf16, 
     fprintf(stderr, "cuTensorMapEncodeTiled rc=%d base=%p inner=%lld outer=%lld pitch=%lld box=%dx%d\n", (int)rc, base, inner,
             outer, pitch_elems, box_inner, box_outer);
   return rc == CUDA_SUCCESS;
+}
+
+// ---- host: im2col-mode TMA descriptor over an NHWC tensor [N, H, W, C] for an R x S filter window ----
+// pad_lo: padding on the low side (the window corner of output pixel 0 sits at -pad_lo); the high-side corner is
+// chosen so that exactly P x Q window positions exist per image.  Pixels are walked W-fastest with `stride`.
+typedef CUresult (*TmaEncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                      const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static inline bool tma_make_map_im2col(CUtensorMap* m, const void* base, bool bf16, int N, int H, int W, int C, int R, int S,
+                                       int P, int Q, int stride, int pad_lo, int channels_per_pixel, int pixels_per_column) {
+  static TmaEncodeIm2colFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<TmaEncodeIm2colFn>(p);
+  }
+  if (!fn) return false;
+  const cuuint64_t es = bf16 ? 2 : 4;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * es, (cuuint64_t)W * C * es, (cuuint64_t)H * W * C * es};
+  // window corners run over [lower, dim + upper): Q positions along W, P along H
+  int lower[2] = {-pad_lo, -pad_lo};
+  int upper[2] = {-pad_lo + (Q - 1) * stride + 1 - W, -pad_lo + (P - 1) * stride + 1 - H};
+  (void)R; (void)S;
+  if (lower[0] < -128 || upper[0] < -128 || upper[1] < -128 || upper[0] > 127 || upper[1] > 127) return false;
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult rc = CUDA_SUCCESS;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    rc = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides,
+            lower, upper, (cuuint32_t)channels_per_pixel, (cuuint32_t)pixels_per_column, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_ERROR_INVALID_CONTEXT || cudaFree(nullptr) != cudaSuccess) break;
+  }
+  if (rc != CUDA_SUCCESS) {
+    if (getenv("B200DDP_DEBUG_TMA"))
+      fprintf(stderr, "cuTensorMapEncodeIm2col rc=%d N=%d H=%d W=%d C=%d P=%d Q=%d stride=%d pad=%d\n", (int)rc, N, H, W, C, P, Q,
+              stride, pad_lo);
+    return false;
+  }
+  // Drivers up to 13.1 mis-encode im2col descriptors of tensors smaller than 128 KB (same correction CUTLASS applies)
+  int driver = 0;
+  if (cudaDriverGetVersion(&driver) == cudaSuccess && driver <= 13010 && (size_t)N * H * W * C * es < 131072)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return true;
 }
 
 // General instruction descriptor for kind::f16 (bf16 operands) / kind::tf32, fp32 accumulation:
