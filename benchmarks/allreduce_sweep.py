@@ -94,7 +94,8 @@ for nbytes in sorted(set(sizes)):
     ref = torch.ones(nbytes // esize, dtype=dtype, device=dev)
     iters = a.iters if nbytes <= (64 << 20) else max(5, a.iters // 4)
     res = {"bytes": nbytes}
-    for algo in ("oneshot", "twoshot"):
+    algos = ("oneshot", "twoshot") + (("nvls",) if comm.arena is not None and comm.arena.multicast else ())
+    for algo in algos:
         if algo == "oneshot" and nbytes > (4 << 20):
             continue
         comm.algo = algo
