@@ -153,12 +153,17 @@ def run_ours(args, rank, local_rank, world):
         native = native_mod
 
     # ---- internal settle (bucket rebuild, graph capture) + W warm-up steps ------------------
+    sampler = ClockSampler(gpu_index=local_rank, period_ms=50).start()     # nvidia-smi takes a while to come up
     for i in range(4 + W):
         step(xs[i % pool_n], pool_y[i % pool_n])
+    sampler.wait_for_samples(1)
+    if K * 1.5 < 300:                      # short run: keep the load on until the sampler has something to show
+        for i in range(64):
+            step(xs[i % pool_n], pool_y[i % pool_n])
     barrier(world)
     launches_before = native.launch_count() if native else 0
     replays_before = step.replays
-    sampler = ClockSampler(gpu_index=local_rank).start()
+    clock_mark = sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(K):
@@ -167,7 +172,7 @@ def run_ours(args, rank, local_rank, world):
     torch.cuda.synchronize()
     barrier(world)
     dev_ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
-    clocks = sampler.stop()
+    clocks = sampler.stop(clock_mark)
     launches = 0
     if native:
         eager_launches = native.launch_count() - launches_before
@@ -298,17 +303,19 @@ def run_reference(args, rank, local_rank, world):
         def __iter__(self):
             it = iter(self.inner)
             ready = [next(it) for _ in range(K + W)]
+            marks["clock"] = ClockSampler(gpu_index=local_rank, period_ms=50).start()
             for i, b in enumerate(ready):
                 if i == W:
                     self._sync()
-                    marks["clock"] = ClockSampler(gpu_index=local_rank).start()
+                    marks["clock"].wait_for_samples(1)
+                    marks["clock_mark"] = marks["clock"].mark()
                     marks["a0"] = torch.cuda.Event(enable_timing=True)
                     marks["a0"].record()
                 yield b
             marks["a1"] = torch.cuda.Event(enable_timing=True)
             marks["a1"].record()
             torch.cuda.synchronize()
-            marks["clocks"] = marks["clock"].stop()
+            marks["clocks"] = marks["clock"].stop(marks.get("clock_mark", 0))
             for i in range(K + W):
                 if i == W:
                     self._sync()

@@ -1142,6 +1142,7 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inne
 }
 
 static bool g_use_tma = true;
+static int g_split_cap = 32;          // upper bound on the split-K factor (per-shape tuning knob, see ops/native.py)
 static bool g_use_im2col_tma = true;
 static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom& g, int channels, int pixels) {
   return tma_make_map_im2col(m, x, bf16, g.Nb, g.H, g.W, g.C, g.R, g.S, g.P, g.Q, g.stride, g.pad, channels, pixels);
@@ -1270,7 +1271,7 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
     // One CTA keeps at most 3 stages (96 KB) of loads in flight, i.e. ~60-100 GB/s at DRAM/L2
     // latency: streaming the operands fast needs MANY CTAs, so K is split until ~128 CTAs run
     // (all co-resident, one per SM: the splits of a tile wait for each other in the epilogue).
-    splits = min(min(128 / tiles, k_blocks / 2), 32);
+    splits = min(min(min(128 / tiles, k_blocks / 2), 32), g_split_cap);
     const size_t per_split = (size_t)tiles * BM * bn * sizeof(float);
     if ((size_t)splits * per_split > workspace_bytes) splits = (int)(workspace_bytes / per_split);
     splits = max(splits, 1);
@@ -1296,6 +1297,7 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 // 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_split_cap(int cap) { b200::tc::g_split_cap = cap < 1 ? 1 : cap; }
 B200_API void b200_gemm_tc_use_im2col_tma(int enabled) { b200::tc::g_use_im2col_tma = enabled != 0; }
 B200_API void b200_gemm_tc_use_2cta(int mode) { b200::tc::g_use_2cta = mode; }   // 0 off, 1 simple, 2 persistent
 

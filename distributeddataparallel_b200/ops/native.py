@@ -122,7 +122,7 @@ _tc_mode = _os.environ.get("B200DDP_TC", "auto")       # auto | 1 (always tcgen0
 _NOT_SUPPORTED = 801          # cudaErrorNotSupported: shape needs the FFMA fallback
 tc_launches = 0
 ffma_launches = 0
-_choice: Dict[tuple, bool] = {}       # (entry point, geometry) -> use tcgen05?
+_choice: Dict[tuple, int] = {}        # (entry point, geometry) -> 0: FFMA kernel, else split-K cap of the tcgen05 kernel
 
 
 def set_tensor_cores(enabled) -> None:
@@ -136,13 +136,23 @@ def tensor_cores_enabled() -> bool:
     return _tc_mode != "0"
 
 
-def conv_choices() -> Dict[tuple, bool]:
+def conv_choices() -> Dict[tuple, int]:
     return dict(_choice)
 
 
-def _launch_tc(name, head, geom, dev) -> int:
+_SPLIT_CAPS = (32, 1, 4)              # split-K upper bounds the tuner tries for a tcgen05 convolution
+
+
+def _launch_tc(name, head, geom, dev, cap: int = 32) -> int:
     s = scratch(dev)
-    return getattr(load_library(), name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+    lib = load_library()
+    if cap == 32:
+        return getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+    lib.b200_gemm_tc_split_cap(_i(cap))            # library-wide knob: restore it for every other GEMM caller
+    try:
+        return getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
+    finally:
+        lib.b200_gemm_tc_split_cap(_i(32))
 
 
 def _launch_ffma(name, head, geom, dev) -> int:
@@ -165,30 +175,31 @@ def _time_variant(fn, iters: int = 3) -> float:
 
 
 def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device) -> None:
-    """Dispatch one convolution pass to the tcgen05 kernel or to the FFMA kernel."""
+    """Dispatch one convolution pass to the tcgen05 kernel (with a tuned split-K bound) or to the FFMA kernel."""
     global _launches, tc_launches, ffma_launches
-    use_tc = _tc_mode == "1"
+    choice = 32 if _tc_mode == "1" else 0          # 0 = FFMA, otherwise the split-K cap of the tcgen05 call
     if _tc_mode == "auto":
         key = (name,) + tuple(g.value for g in geom)
-        use_tc = _choice.get(key)
-        if use_tc is None:
+        choice = _choice.get(key)
+        if choice is None:
             if torch.cuda.is_current_stream_capturing():
-                use_tc = False                       # cannot time inside a capture: stay on the safe path
+                choice = 0                           # cannot time inside a capture: stay on the safe path
             else:
-                # time both on the real operands; statistics / accumulation are switched off while
+                # time the variants on the real operands; statistics / accumulation are switched off while
                 # timing so the repeated runs have no side effects beyond rewriting the output
                 quiet = head[:3] + (_ptr(None),) if name == "b200_conv2d_fprop" else head
                 if name == "b200_conv2d_wgrad":
                     quiet = head[:3] + (_i(0),)
+                choice = 0
                 if _launch_tc(name, quiet, geom, dev) == 0:
-                    t_tc = _time_variant(lambda: _launch_tc(name, quiet, geom, dev))
-                    t_ff = _time_variant(lambda: _launch_ffma(name, quiet, geom, dev))
-                    use_tc = t_tc < t_ff
-                else:
-                    use_tc = False
-                _choice[key] = use_tc
-    if use_tc:
-        rc = _launch_tc(name, head, geom, dev)
+                    best = _time_variant(lambda: _launch_ffma(name, quiet, geom, dev), 5)
+                    for cap in _SPLIT_CAPS:
+                        t = _time_variant(lambda: _launch_tc(name, quiet, geom, dev, cap), 5)
+                        if t < best:
+                            best, choice = t, cap
+                _choice[key] = choice
+    if choice:
+        rc = _launch_tc(name, head, geom, dev, choice)
         if rc == 0:
             _launches += 1
             tc_launches += 1

@@ -42,7 +42,20 @@ class ClockSampler:
         self._thread.start()
         return self
 
-    def stop(self) -> Dict:
+    def mark(self) -> int:
+        """Number of samples taken so far: pass it to ``stop`` / ``summary`` to summarise only what came after
+        (start the sampler early -- nvidia-smi needs up to a second to come up on an 8-GPU box -- and mark the
+        beginning of the timed region)."""
+        return len(self._lines)
+
+    def wait_for_samples(self, n: int = 1, timeout_s: float = 3.0) -> None:
+        import time
+
+        t0 = time.time()
+        while self._proc is not None and len(self._lines) < n and time.time() - t0 < timeout_s:
+            time.sleep(0.02)
+
+    def stop(self, first: int = 0) -> Dict:
         if self._proc is not None:
             self._proc.terminate()
             try:
@@ -51,11 +64,14 @@ class ClockSampler:
                 self._proc.kill()
         if self._thread is not None:
             self._thread.join(timeout=2)
-        return self.summary()
+        return self.summary(first)
 
-    def summary(self) -> Dict:
+    def summary(self, first: int = 0) -> Dict:
         sm, mx, power, reasons = [], [], [], set()
-        for line in self._lines:
+        lines = self._lines[first:]
+        if not lines:                      # region shorter than one sampling period: the samples just before it
+            lines = self._lines[-3:]       # (warm-up, same load) are the closest evidence there is
+        for line in lines:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 9:
                 continue
