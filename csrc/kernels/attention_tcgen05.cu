@@ -29,6 +29,8 @@
 #include <cuda_bf16.h>
 #include <math.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "tcgen05.cuh"
 #include "b200ddp.h"
@@ -151,10 +153,11 @@ attn_fwd_kernel(const FwdArgs a, const __grid_constant__ CUtensorMap map_qkv) {
     for (int i = 0; i < 64; ++i) o[i] = 0.f;
     uint32_t r[32];
 
-    for (int j = 0; j < nkv; ++j) {
+    // one key block; DIAG (compile time) = the block on the diagonal, the only one that needs the causal mask
+    auto block = [&](int j, auto diag_tag) {
+      constexpr bool DIAG = decltype(diag_tag)::value;
       mbar_wait(&s_full, j & 1, a.error);
       tc_fence_after();
-      const bool diag = j == qb;
       float mx = -INFINITY;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
@@ -163,7 +166,7 @@ attn_fwd_kernel(const FwdArgs a, const __grid_constant__ CUtensorMap map_qkv) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float v = __uint_as_float(r[i]);
-          if (!diag || c * 32 + i <= row) mx = fmaxf(mx, v);
+          if (!DIAG || c * 32 + i <= row) mx = fmaxf(mx, v);
         }
       }
       const float m_new = fmaxf(m, mx * a.scale_log2);
@@ -189,8 +192,8 @@ attn_fwd_kernel(const FwdArgs a, const __grid_constant__ CUtensorMap map_qkv) {
         for (int i = 0; i < 32; i += 2) {
           float p0 = exp2f(__uint_as_float(r[i]) * a.scale_log2 - m_new);
           float p1 = exp2f(__uint_as_float(r[i + 1]) * a.scale_log2 - m_new);
-          if (diag && c * 32 + i > row) p0 = 0.f;
-          if (diag && c * 32 + i + 1 > row) p1 = 0.f;
+          if (DIAG && c * 32 + i > row) p0 = 0.f;
+          if (DIAG && c * 32 + i + 1 > row) p1 = 0.f;
           sum += p0 + p1;
           w[i >> 1] = pack_bf16x2(p0, p1);
         }
@@ -205,7 +208,9 @@ attn_fwd_kernel(const FwdArgs a, const __grid_constant__ CUtensorMap map_qkv) {
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full);
-    }
+    };
+    for (int j = 0; j < nkv - 1; ++j) block(j, std::false_type{});
+    block(nkv - 1, std::true_type{});
     mbar_wait(&o_full, (nkv - 1) & 1, a.error);
     tc_fence_after();
     const float inv = 1.f / l;
@@ -360,15 +365,15 @@ attn_bwd_kernel(const BwdArgs a, const __grid_constant__ CUtensorMap map_qkv, co
       }
     };
 
-    for (int it = 0; it < n_it; ++it) {
+    auto block = [&](int it, auto diag_tag) {
+      constexpr bool DIAG = decltype(diag_tag)::value;
       const int qrow = (jb + it) * 128 + row;
       const bool valid = qrow < a.T;
       const float L = valid ? __ldg(a.lse + (size_t)bh * a.T + qrow) : INFINITY;
-      const float Dr = valid ? __ldg(a.delta + (size_t)bh * a.T + qrow) : 0.f;
+      const float Ds = valid ? __ldg(a.delta + (size_t)bh * a.T + qrow) * a.scale : 0.f;
       if (it > 0) flush_dq(it - 1);
       mbar_wait(&sdp_full, it & 1, a.error);
       tc_fence_after();
-      const bool diag = it == 0;
 #pragma unroll 1
       for (int c = 0; c < 2; ++c) {
         const int col0 = hf * 64 + c * 32;
@@ -379,7 +384,7 @@ attn_bwd_kernel(const BwdArgs a, const __grid_constant__ CUtensorMap map_qkv, co
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           p[i] = exp2f(__uint_as_float(r[i]) * a.scale_log2 - L);
-          if (diag && col0 + i > row) p[i] = 0.f;
+          if (DIAG && col0 + i > row) p[i] = 0.f;
         }
 #pragma unroll
         for (int i = 0; i < 16; ++i) w[i] = pack_bf16x2(p[2 * i], p[2 * i + 1]);
@@ -389,9 +394,9 @@ attn_bwd_kernel(const BwdArgs a, const __grid_constant__ CUtensorMap map_qkv, co
         tmem_ld32_nowait(tdP + lane_addr + col0, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-          w[i] = pack_bf16x2(p[2 * i] * (__uint_as_float(r[2 * i]) - Dr) * a.scale,
-                             p[2 * i + 1] * (__uint_as_float(r[2 * i + 1]) - Dr) * a.scale);
+        for (int i = 0; i < 16; ++i)                   // dS = P * (dP - D) / sqrt(d), the scale folded into one FMA
+          w[i] = pack_bf16x2(p[2 * i] * (__uint_as_float(r[2 * i]) * a.scale - Ds),
+                             p[2 * i + 1] * (__uint_as_float(r[2 * i + 1]) * a.scale - Ds));
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           st_shared_v4(p_chunk(sdS, row, (col0 >> 3) + q), w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
@@ -400,7 +405,9 @@ attn_bwd_kernel(const BwdArgs a, const __grid_constant__ CUtensorMap map_qkv, co
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(&pds_full);
-    }
+    };
+    block(0, std::true_type{});                            // the first query block is the diagonal one
+    for (int it = 1; it < n_it; ++it) block(it, std::false_type{});
     flush_dq(n_it - 1);                                    // also means every MMA of this CTA has completed
     const int krow = jb * 128 + row;
 #pragma unroll
