@@ -372,7 +372,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
     const bool any_gather = gather_a || gather_b;
     // TMA boxes: K-major operand = one box [ROWS x 128 B]; bf16 MN-major operand = ROWS/64 boxes of
     // [64 k rows x 128 B of mn], 8 KB each.  Both land in the SWIZZLE_128B layout the MMA expects.
-    const uint32_t tx_bytes = (a.tma_a ? (uint32_t)A_STAGE : 0u) + (a.tma_b ? (uint32_t)B_STAGE : 0u);
+    // wgrad activations by im2col-mode TMA (tma_b == 4): one [32 pixels x 32 channels] box per 32 output columns
+    // (= 32 channels of one filter tap); boxes past the last column are not fetched
+    const int b_boxes = a.tma_b == 4 ? min(BN / 32, (a.N - n0 + 31) / 32) : 0;
+    const uint32_t tx_bytes = (a.tma_a ? (uint32_t)A_STAGE : 0u) +
+                              (a.tma_b == 4 ? (uint32_t)b_boxes * 4096u : (a.tma_b ? (uint32_t)B_STAGE : 0u));
     // im2col-mode TMA: window corner (w, h, n) of the tile's first output pixel
     int im_w_a = 0, im_h_a = 0, im_n_a = 0, im_w_b = 0, im_h_b = 0, im_n_b = 0;
     if (t == 0 && a.tma_a == 2) {
@@ -406,6 +410,25 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
             if (a.tma_b == 2)
               tma_load_im2col_4d(smem_b + s * B_STAGE, &map_b, c0, im_w_b, im_h_b, im_n_b, (unsigned short)sx, (unsigned short)r, &full_bar[s]);
           }
+          // fp32 MN-major by TMA: boxes of [32 k rows x 32 mn] (4 KB) in the SWIZZLE_128B_ATOM_32B pattern, which is
+          // the 128B_BASE32B layout the tensor core reads (32-byte units XOR-ed with the k row, bits [5,7) ^= [7,9))
+          if (a.tma_b == 4) {                              // k0 = first output pixel of this k-block
+            int t1, q, p, img;
+            a.g.fQ.divmod(k0, t1, q);
+            a.g.fP.divmod(t1, img, p);
+            const int w0 = q * a.g.stride - a.g.pad, h0 = p * a.g.stride - a.g.pad;
+            for (int bx = 0; bx < b_boxes; ++bx) {
+              int rs, c0, r, sx;
+              a.g.fC.divmod(n0 + bx * 32, rs, c0);
+              a.g.fS.divmod(rs, r, sx);
+              tma_load_im2col_4d(smem_b + s * B_STAGE + bx * 4096, &map_b, c0, w0, h0, img, (unsigned short)sx, (unsigned short)r,
+                                 &full_bar[s]);
+            }
+          }
+          if (a.tma_a == 3)
+            for (int bx = 0; bx < BM / 32; ++bx) tma_load_2d(smem_a + s * A_STAGE + bx * 4096, &map_a, m0 + bx * 32, k0, &full_bar[s]);
+          if (a.tma_b == 3)
+            for (int bx = 0; bx < BN / 32; ++bx) tma_load_2d(smem_b + s * B_STAGE + bx * 4096, &map_b, n0 + bx * 32, k0, &full_bar[s]);
           if (a.tma_a == 1) {
             if (!is_mn(AK)) tma_load_2d(smem_a + s * A_STAGE, &map_a, k0, m0, &full_bar[s]);
             else
@@ -462,9 +485,11 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         // a TMA-fetched bf16 MN-major operand sits in the SWIZZLE_128B MN-major layout instead:
         // 64-mn atoms 8 KB apart (LBO), 8-k-row atoms 1 KB apart (SBO), 2 k-atoms per MMA
         const bool a_mn_tma = is_mn(AK) && a.tma_a == 1, b_mn_tma = is_mn(BK_) && a.tma_b == 1;
-        const uint64_t da = a_mn_tma ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
+        const uint64_t da = a.tma_a == 3 ? make_desc(smem_a + s * A_STAGE + j * 1024, 4096, 512, 1u)
+                          : a_mn_tma ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
                                      : make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
-        const uint64_t db = b_mn_tma ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
+        const uint64_t db = a.tma_b >= 3 ? make_desc(smem_b + s * B_STAGE + j * 1024, 4096, 512, 1u)
+                          : b_mn_tma ? make_desc(smem_b + s * B_STAGE + j * 2048, 8192, 1024, 2u)
                                      : make_desc(smem_b + s * B_STAGE + j * B_STEP, B_LBO, B_SBO, B_TYPE);
         umma<BF16>(tmem_d, da, db, idesc, (kb | j) ? 1u : 0u);
       }
@@ -1144,6 +1169,7 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inne
 static bool g_use_tma = true;
 static int g_split_cap = 32;          // upper bound on the split-K factor (per-shape tuning knob, see ops/native.py)
 static bool g_use_im2col_tma = true;
+static bool g_use_mn32_tma = true;    // fp32 MN-major operands by TMA (SWIZZLE_128B_ATOM_32B)
 static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom& g, int channels, int pixels) {
   return tma_make_map_im2col(m, x, bf16, g.Nb, g.H, g.W, g.C, g.R, g.S, g.P, g.Q, g.stride, g.pad, channels, pixels);
 }
@@ -1159,8 +1185,16 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     // dense K-major: matrix [rows x K]; dense bf16 MN-major: matrix [K x mn], boxes of 64 mn x KELEMS k
     if (AK == DENSE_K) a.tma_a = make_map(&map_a, a.a, BF16, a.Kd, a.M, a.lda, KELEMS, BM);
     else if (AK == DENSE_MN && BF16) a.tma_a = make_map(&map_a, a.a, true, a.M, a.Kd, a.lda, 64, KELEMS);
+    else if (AK == DENSE_MN && g_use_mn32_tma &&
+             tma_make_map_2d(&map_a, a.a, false, a.M, a.Kd, a.lda, 32, KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) a.tma_a = 3;
     if (BK_ == DENSE_K) a.tma_b = make_map(&map_b, a.b, BF16, a.Kd, a.N, a.ldb, KELEMS, BN);
     else if (BK_ == DENSE_MN && BF16 && BN >= 64) a.tma_b = make_map(&map_b, a.b, true, a.N, a.Kd, a.ldb, 64, KELEMS);
+    else if (BK_ == DENSE_MN && !BF16 && g_use_mn32_tma &&
+             tma_make_map_2d(&map_b, a.b, false, a.N, a.Kd, a.ldb, 32, KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) a.tma_b = 3;
+    if (BK_ == IM2COL_MN && !BF16 && g_use_im2col_tma && g_use_mn32_tma && a.g.C % 32 == 0 &&
+        tma_make_map_im2col(&map_b, a.b, false, a.g.Nb, a.g.H, a.g.W, a.g.C, a.g.R, a.g.S, a.g.P, a.g.Q, a.g.stride, a.g.pad, 32,
+                            KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
+      a.tma_b = 4;
     // convolution activations: im2col-mode TMA when a k-block never straddles a filter tap
     if (g_use_im2col_tma && a.g.C % KELEMS == 0) {
       if (AK == IM2COL_K && make_im2col_map(&map_a, a.a, BF16, a.g, KELEMS, BM)) a.tma_a = 2;
@@ -1297,6 +1331,7 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 // 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_use_mn32_tma(int enabled) { b200::tc::g_use_mn32_tma = enabled != 0; }
 B200_API void b200_gemm_tc_split_cap(int cap) { b200::tc::g_split_cap = cap < 1 ? 1 : cap; }
 B200_API void b200_gemm_tc_use_im2col_tma(int enabled) { b200::tc::g_use_im2col_tma = enabled != 0; }
 B200_API void b200_gemm_tc_use_2cta(int mode) { b200::tc::g_use_2cta = mode; }   // 0 off, 1 simple, 2 persistent

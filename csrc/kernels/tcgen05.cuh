@@ -155,7 +155,8 @@ static inline TmaEncodeTiledFn tma_encode_fn() {
   return fn;
 }
 static inline bool tma_make_map_2d(CUtensorMap* m, const void* base, bool bf16, long long inner, long long outer,
-                                   long long pitch_elems, int box_inner, int box_outer) {
+                                   long long pitch_elems, int box_inner, int box_outer,
+                                   CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   TmaEncodeTiledFn fn = tma_encode_fn();
   if (!fn) return false;
   const int es = bf16 ? 2 : 4;
@@ -166,7 +167,7 @@ static inline bool tma_make_map_2d(CUtensorMap* m, const void* base, bool bf16, 
   CUresult rc = CUDA_SUCCESS;
   for (int attempt = 0; attempt < 2; ++attempt) {
     rc = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
-            const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     // A thread that has made no runtime call yet (autograd's backward thread on its first op) has no
     // current context for this driver call: bind the primary context and try once more.
@@ -185,7 +186,8 @@ typedef CUresult (*TmaEncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint3
                                       const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
                                       CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static inline bool tma_make_map_im2col(CUtensorMap* m, const void* base, bool bf16, int N, int H, int W, int C, int R, int S,
-                                       int P, int Q, int stride, int pad_lo, int channels_per_pixel, int pixels_per_column) {
+                                       int P, int Q, int stride, int pad_lo, int channels_per_pixel, int pixels_per_column,
+                                       CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   static TmaEncodeIm2colFn fn = nullptr;
   static bool tried = false;
   if (!tried) {
@@ -210,7 +212,7 @@ static inline bool tma_make_map_im2col(CUtensorMap* m, const void* base, bool bf
   for (int attempt = 0; attempt < 2; ++attempt) {
     rc = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides,
             lower, upper, (cuuint32_t)channels_per_pixel, (cuuint32_t)pixels_per_column, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (rc != CUDA_ERROR_INVALID_CONTEXT || cudaFree(nullptr) != cudaSuccess) break;
   }
   if (rc != CUDA_SUCCESS) {
