@@ -90,6 +90,48 @@ __global__ void __launch_bounds__(256) colsum_bf16_acc_kernel(const __nv_bfloat1
   }
 }
 
+// bias gradient of a bf16 Linear in one launch: column sums of a tall [M, N] bf16 matrix -> bf16 [N].
+// Rows are split over blockIdx.y; partial sums go to a zero-on-entry fp32 accumulator; the last block (ticket)
+// converts, writes the result and re-zeroes accumulator and ticket.
+__global__ void __launch_bounds__(256) colsum_bf16_fused_kernel(const __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ out,
+                                                                float* __restrict__ acc, unsigned* __restrict__ ticket, int M,
+                                                                int N, int rows_per_block) {
+  const int n = blockIdx.x * 64 + (threadIdx.x & 31) * 2;
+  const int r0 = blockIdx.y * rows_per_block + (threadIdx.x >> 5);
+  const int r1 = min(M, (blockIdx.y + 1) * rows_per_block);
+  __shared__ float sh[8][64];
+  __shared__ unsigned last_s;
+  float s0 = 0.f, s1 = 0.f;
+  if (n + 1 < N) {
+    for (int m = r0; m < r1; m += 8) {
+      const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(a + (size_t)m * N + n);
+      s0 += __bfloat162float(v.x);
+      s1 += __bfloat162float(v.y);
+    }
+  }
+  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2] = s0;
+  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64 && blockIdx.x * 64 + threadIdx.x < N) {
+    float tot = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) tot += sh[r][threadIdx.x];
+    atomicAdd(acc + blockIdx.x * 64 + threadIdx.x, tot);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last_s = atomicAdd(ticket, 1u) == gridDim.x * gridDim.y - 1 ? 1u : 0u;
+  __syncthreads();
+  if (last_s) {
+    __threadfence();
+    for (int j = threadIdx.x; j < N; j += 256) {
+      out[j] = __float2bfloat16_rn(__ldcg(acc + j));
+      acc[j] = 0.f;
+    }
+    if (threadIdx.x == 0) *ticket = 0u;
+  }
+}
+
 // bf16 variant of colsum (bias gradients of bf16 Linear layers)
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ out,
                                                           int M, int N, int accumulate) {
@@ -151,5 +193,15 @@ B200_API int b200_colsum_bf16_acc(const void* a, float* acc, int M, int N, cudaS
   const int rows_per_block = 256;
   dim3 grid(ceil_div(N, 64), ceil_div(M, rows_per_block));
   colsum_bf16_acc_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a), acc, M, N, rows_per_block);
+  B200_LAUNCH_CHECK();
+}
+
+// acc: fp32 [>= N], ticket: one word; both zero on entry, left zero on exit.  N must be even.
+B200_API int b200_colsum_bf16_fused(const void* a, void* out, float* acc, unsigned* ticket, int M, int N, cudaStream_t stream) {
+  if (N % 2) return static_cast<int>(cudaErrorInvalidValue);
+  const int rows_per_block = 256;
+  dim3 grid(ceil_div(N, 64), ceil_div(M, rows_per_block));
+  colsum_bf16_fused_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a), static_cast<__nv_bfloat16*>(out), acc,
+                                                     ticket, M, N, rows_per_block);
   B200_LAUNCH_CHECK();
 }

@@ -126,6 +126,110 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const T* __restrict_
   }
 }
 
+// ---- bf16 LayerNorm backward, one pass, everything fused -------------------------------------------------
+// D = NV * 256: lane l of a warp owns columns v*256 + l*8 .. +8 (16-byte loads, a warp reads 512 contiguous bytes).
+// Per row: dx = rstd * (dy*gamma - mean(dy*gamma) - xhat * mean(dy*gamma*xhat)) [+ dres, the gradient arriving on
+// the residual branch that bypasses the LayerNorm].  dgamma / dbeta partials stay in registers over all rows of a
+// warp, are combined per block in shared memory, added to a zero-on-entry fp32 accumulator, and the LAST block
+// (ticket) writes the bf16 results and re-zeroes accumulator and ticket -- no memset / cast launches around it.
+template <int NV>
+__global__ void __launch_bounds__(256, 1)
+layernorm_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                          const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres,
+                          __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dgamma, __nv_bfloat16* __restrict__ dbeta,
+                          float* __restrict__ acc, unsigned* __restrict__ ticket, int M) {
+  constexpr int D = NV * 256;
+  __shared__ float sh[2 * D];
+  __shared__ float gs[D];
+  __shared__ unsigned last_s;
+  for (int j = threadIdx.x; j < 2 * D; j += 256) sh[j] = 0.f;
+  for (int j = threadIdx.x; j < D; j += 256) gs[j] = __bfloat162float(gamma[j]);
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  float pg[NV * 8], pb[NV * 8];
+#pragma unroll
+  for (int i = 0; i < NV * 8; ++i) pg[i] = pb[i] = 0.f;
+  const float inv_d = 1.f / (float)D;
+  for (int row = blockIdx.x * 8 + w; row < M; row += gridDim.x * 8) {
+    uint4 xv[NV], dv[NV];
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
+    const uint4* gr = reinterpret_cast<const uint4*>(dy + (size_t)row * D);
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      xv[v] = xr[v * 32 + lane];
+      dv[v] = gr[v * 32 + lane];
+    }
+    const float mu = mean[row], rs = rstd[row];
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[v]);
+      const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[v]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]);
+        const int c = v * 256 + lane * 8 + 2 * e;
+        const float g0 = df.x * gs[c], g1 = df.y * gs[c + 1];
+        a += g0 + g1;
+        b += g0 * ((xf.x - mu) * rs) + g1 * ((xf.y - mu) * rs);
+      }
+    }
+    a = warp_sum(a) * inv_d;
+    b = warp_sum(b) * inv_d;
+    uint4* dr = reinterpret_cast<uint4*>(dx + (size_t)row * D);
+    const uint4* rr = dres ? reinterpret_cast<const uint4*>(dres + (size_t)row * D) : nullptr;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[v]);
+      const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[v]);
+      uint4 rv = make_uint4(0, 0, 0, 0);
+      if (rr) rv = rr[v * 32 + lane];
+      const __nv_bfloat162* rh2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
+      uint32_t o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]), rf = __bfloat1622float2(rh2[e]);
+        const int c = v * 256 + lane * 8 + 2 * e;
+        const float h0 = (xf.x - mu) * rs, h1 = (xf.y - mu) * rs;
+        const float o0 = rs * (df.x * gs[c] - a - h0 * b) + rf.x;
+        const float o1 = rs * (df.y * gs[c + 1] - a - h1 * b) + rf.y;
+        pg[v * 8 + 2 * e] += df.x * h0;
+        pg[v * 8 + 2 * e + 1] += df.y * h1;
+        pb[v * 8 + 2 * e] += df.x;
+        pb[v * 8 + 2 * e + 1] += df.y;
+        const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
+        o[e] = *reinterpret_cast<const uint32_t*>(&ob);
+      }
+      dr[v * 32 + lane] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = v * 256 + lane * 8 + e;
+      atomicAdd(&sh[c], pg[v * 8 + e]);
+      atomicAdd(&sh[D + c], pb[v * 8 + e]);
+    }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * D; j += 256) atomicAdd(acc + j, sh[j]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last_s = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (last_s) {                                            // every block's additions are visible: finish up
+    __threadfence();
+    for (int j = threadIdx.x; j < D; j += 256) {
+      dgamma[j] = __float2bfloat16_rn(__ldcg(acc + j));
+      dbeta[j] = __float2bfloat16_rn(__ldcg(acc + D + j));
+      acc[j] = 0.f;
+      acc[D + j] = 0.f;
+    }
+    if (threadIdx.x == 0) *ticket = 0u;
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) scale_any_kernel(T* __restrict__ x, size_t n, const float* __restrict__ scale_dev) {
   const float sc = __ldg(scale_dev);
@@ -377,6 +481,24 @@ B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma
 B200_API int b200_cast_from_f32(const float* in, void* out, size_t n, int accumulate, int is_bf16, cudaStream_t st) {
   B200_DISPATCH(is_bf16, (cast_from_f32_kernel<float><<<grid1d(n), 256, 0, st>>>(in, (float*)out, n, accumulate)),
                 (cast_from_f32_kernel<bf16><<<grid1d(n), 256, 0, st>>>(in, (bf16*)out, n, accumulate)));
+  B200_LAUNCH_CHECK();
+}
+
+// bf16, D in {768, 1024, 1280}: dx (+ dres), dgamma, dbeta in ONE launch.  acc: fp32 [2*D] and ticket: one word,
+// both zero on entry and left zero on exit (persistent scratch owned by the caller, one per stream).
+// Returns cudaErrorNotSupported (801) for other widths (use b200_layernorm_bwd).
+B200_API int b200_layernorm_bwd_fused(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                                      const void* dres, void* dx, void* dgamma, void* dbeta, float* acc, unsigned* ticket,
+                                      int M, int D, cudaStream_t st) {
+  const int grid = min(ceil_div(M, 8), kNumSMs);          // ~170 registers: one 8-warp block per SM
+#define B200_LN_BWD(NV)                                                                                               \
+  layernorm_bwd_bf16_kernel<NV><<<grid, 256, 0, st>>>((const bf16*)dy, (const bf16*)x, (const bf16*)gamma, mean, rstd, \
+                                                      (const bf16*)dres, (bf16*)dx, (bf16*)dgamma, (bf16*)dbeta, acc, ticket, M)
+  if (D == 768) B200_LN_BWD(3);
+  else if (D == 1024) B200_LN_BWD(4);
+  else if (D == 1280) B200_LN_BWD(5);
+  else return static_cast<int>(cudaErrorNotSupported);
+#undef B200_LN_BWD
   B200_LAUNCH_CHECK();
 }
 

@@ -85,11 +85,13 @@ class Block(nn.Module):
         if _native(x) and self.c_fc.bias is not None:
             from ..ops import native_tf
 
-            # residual adds, GELU and its derivative ride in GEMM epilogues
-            a = self.attention(self.c_attn(self.ln_1(x)))
-            x = native_tf.linear_tc(a, self.c_proj.weight, self.c_proj.bias, residual=x)
-            return native_tf.mlp(self.ln_2(x), self.c_fc.weight, self.c_fc.bias, self.c_proj2.weight,
-                                 self.c_proj2.bias, residual=x)
+            # residual adds, GELU and its derivative ride in GEMM epilogues; the residual branches' gradients
+            # are added inside the LayerNorm backward kernels
+            h, xr = native_tf.layer_norm_res(x, self.ln_1.weight, self.ln_1.bias, self.ln_1.eps)
+            a = self.attention(self.c_attn(h))
+            x = native_tf.linear_tc(a, self.c_proj.weight, self.c_proj.bias, residual=xr)
+            h, xr = native_tf.layer_norm_res(x, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps)
+            return native_tf.mlp(h, self.c_fc.weight, self.c_fc.bias, self.c_proj2.weight, self.c_proj2.bias, residual=xr)
         x = x + self.c_proj(self.attention(self.c_attn(self.ln_1(x))))
         h = F.gelu(self.c_fc(self.ln_2(x)), approximate="tanh")
         return x + self.c_proj2(h)

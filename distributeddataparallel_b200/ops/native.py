@@ -97,6 +97,9 @@ class _Scratch:
         self.counters = torch.zeros(self.MAX_COUNTERS, dtype=torch.int32, device=device)
         self.row_loss = torch.empty(1 << 16, dtype=torch.float32, device=device)
         self.error = torch.zeros(16, dtype=torch.int32, device=device)     # tcgen05 wait-timeout word
+        # zero-on-entry / zero-on-exit accumulators of the one-launch reductions (LayerNorm backward, bias gradients)
+        self.red_acc = torch.zeros(32768, dtype=torch.float32, device=device)
+        self.red_ticket = torch.zeros(4, dtype=torch.int32, device=device)
 
 
 _scratch: Dict[int, _Scratch] = {}

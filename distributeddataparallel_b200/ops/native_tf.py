@@ -66,6 +66,10 @@ def gemm_epi(a, b, out, mode: int, m: int, n: int, k: int, lda: int, ldb: int, l
 def _bias_grad(dy2, param, slot):
     m, n = dy2.shape
     db, _ = _grad_target(param, slot, param)
+    sc = scratch(dy2.device)
+    if _bf(dy2) and db.dtype == torch.bfloat16 and m >= 1024 and n % 2 == 0 and n <= sc.red_acc.numel() and db.is_contiguous():
+        _call("b200_colsum_bf16_fused", _ptr(dy2), _ptr(db), _ptr(sc.red_acc), _ptr(sc.red_ticket), _i(m), _i(n), _stream())
+        return db
     if _bf(dy2) and m >= 1024 and n % 2 == 0:
         acc = torch.zeros(n, dtype=torch.float32, device=dy2.device)
         _call("b200_colsum_bf16_acc", _ptr(dy2), _ptr(acc), _i(m), _i(n), _stream())
@@ -189,8 +193,11 @@ def mlp(x, w1, b1, w2, b2, residual):
 
 # ---------------------------------------------------------------------------------------------
 class _LayerNorm(torch.autograd.Function):
+    """y = LayerNorm(x).  With ``with_residual`` the Function also hands back an alias of ``x`` for the residual
+    branch, so that branch's gradient comes back into this backward and is added inside the kernel."""
+
     @staticmethod
-    def forward(ctx, x, gamma, beta, eps):
+    def forward(ctx, x, gamma, beta, eps, with_residual=False):
         x2 = x.reshape(-1, x.shape[-1]).contiguous()
         m, d = x2.shape
         y = torch.empty_like(x2)
@@ -202,26 +209,47 @@ class _LayerNorm(torch.autograd.Function):
         ctx.shape = x.shape
         ctx.params = (gamma, beta)
         ctx.slots = (getattr(gamma, "_grad_slot", None), getattr(beta, "_grad_slot", None))
+        ctx.with_residual = with_residual
+        if with_residual:
+            return y.reshape(x.shape), x2.view(x.shape)
         return y.reshape(x.shape)
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dres=None):
         x2, gamma, mean, rstd = ctx.saved_tensors
         m, d = x2.shape
         dy2 = dy.reshape(m, d).contiguous()
         dx = torch.empty_like(x2)
-        acc = torch.zeros(2 * d, dtype=torch.float32, device=dy.device)
-        _call("b200_layernorm_bwd", _ptr(dy2), _ptr(x2), _ptr(gamma), _ptr(mean), _ptr(rstd), _ptr(dx), _ptr(acc),
-              _ptr(acc[d:]), _i(m), _i(d), _i(_bf(x2)), _stream())
         dgamma, _ = _grad_target(ctx.params[0], ctx.slots[0], gamma)
         dbeta, _ = _grad_target(ctx.params[1], ctx.slots[1], gamma)
-        _call("b200_cast_from_f32", _ptr(acc), _ptr(dgamma), _sz(d), _i(0), _i(_bf(gamma)), _stream())
-        _call("b200_cast_from_f32", _ptr(acc[d:]), _ptr(dbeta), _sz(d), _i(0), _i(_bf(gamma)), _stream())
-        return dx.reshape(ctx.shape), dgamma, dbeta, None
+        if dres is not None:
+            dres = dres.reshape(m, d)
+            if not dres.is_contiguous():
+                dres = dres.contiguous()
+        sc = scratch(dy.device)
+        fused = (_bf(x2) and gamma.dtype == torch.bfloat16 and dgamma.is_contiguous() and dbeta.is_contiguous()
+                 and _try_call("b200_layernorm_bwd_fused", _ptr(dy2), _ptr(x2), _ptr(gamma), _ptr(mean), _ptr(rstd), _ptr(dres),
+                               _ptr(dx), _ptr(dgamma), _ptr(dbeta), _ptr(sc.red_acc), _ptr(sc.red_ticket[1:]), _i(m), _i(d),
+                               _stream()) == 0)
+        if not fused:
+            acc = torch.zeros(2 * d, dtype=torch.float32, device=dy.device)
+            _call("b200_layernorm_bwd", _ptr(dy2), _ptr(x2), _ptr(gamma), _ptr(mean), _ptr(rstd), _ptr(dx), _ptr(acc),
+                  _ptr(acc[d:]), _i(m), _i(d), _i(_bf(x2)), _stream())
+            _call("b200_cast_from_f32", _ptr(acc), _ptr(dgamma), _sz(d), _i(0), _i(_bf(gamma)), _stream())
+            _call("b200_cast_from_f32", _ptr(acc[d:]), _ptr(dbeta), _sz(d), _i(0), _i(_bf(gamma)), _stream())
+            if dres is not None:
+                dx = dx + dres
+        return dx.reshape(ctx.shape), dgamma, dbeta, None, None
 
 
 def layer_norm(x, weight, bias, eps=1e-5):
     return _LayerNorm.apply(x, weight, bias, float(eps))
+
+
+def layer_norm_res(x, weight, bias, eps=1e-5):
+    """(LayerNorm(x), x): use the second result for the residual connection around the normalised branch --
+    its gradient is then added to the LayerNorm input gradient inside the backward kernel."""
+    return _LayerNorm.apply(x, weight, bias, float(eps), True)
 
 
 class _Gelu(torch.autograd.Function):

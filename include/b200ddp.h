@@ -98,6 +98,8 @@ int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, flo
 int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
 int b200_colsum(const float* a, float* out, int M, int N, int accumulate, cudaStream_t stream);
 int b200_colsum_bf16(const void* a, void* out, int M, int N, int accumulate, cudaStream_t stream);
+/* one-launch bias gradient: acc (fp32 [>= N]) and ticket (1 word) are zero on entry and left zero on exit */
+int b200_colsum_bf16_fused(const void* a, void* out, float* acc, unsigned* ticket, int M, int N, cudaStream_t stream);
 int b200_colsum_bf16_acc(const void* a, float* acc, int M, int N, cudaStream_t stream);   /* tall matrices: fp32 atomics */
 
 /* ---- fused multi-tensor optimizers (optim.SGD at REF:41,53) -------------------------
@@ -154,6 +156,11 @@ int b200_conv2d_wgrad_tc(const float* dy, const float* x, float* dw, int accumul
 /* ---- transformer blocks (GPT-2 configuration): fp32 math on fp32 / bf16 storage -------- */
 int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
                        int M, int D, float eps, int is_bf16, cudaStream_t st);
+/* bf16, D in {768, 1024, 1280}: dx (+ dres: gradient of the residual branch), dgamma, dbeta in one launch; acc
+ * (fp32 [2*D]) and ticket (1 word) zero on entry, left zero on exit; 801 for other widths */
+int b200_layernorm_bwd_fused(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                             const void* dres, void* dx, void* dgamma, void* dbeta, float* acc, unsigned* ticket, int M,
+                             int D, cudaStream_t st);
 int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                        void* dx, float* dgamma_acc, float* dbeta_acc, int M, int D, int is_bf16, cudaStream_t st);
 int b200_cast_from_f32(const float* in, void* out, size_t n, int accumulate, int is_bf16, cudaStream_t st);

@@ -146,3 +146,32 @@ def test_linear_residual_epilogue():
     ref = x.float() @ w.float().t() + b.float() + r.detach().float()
     assert _rel(y, ref) < 1e-2
     assert torch.equal(r.grad, torch.ones_like(r))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("d_model", [768, 1024, 1280, 512])
+def test_layernorm_with_residual_branch_and_one_launch_bias_grad(d_model):
+    """LayerNorm whose backward also absorbs the residual branch's gradient (fused widths 768/1024/1280, generic
+    kernels otherwise), and the one-launch bf16 bias gradient, against fp32 references; run twice to check the
+    zero-on-exit accumulators."""
+    from distributeddataparallel_b200.ops import native_tf
+
+    torch.manual_seed(21)
+    m = 2048
+    for _ in range(2):
+        x = torch.randn(m, d_model, device="cuda").to(torch.bfloat16).requires_grad_(True)
+        g = (1 + 0.1 * torch.randn(d_model, device="cuda")).to(torch.bfloat16).requires_grad_(True)
+        b = (0.1 * torch.randn(d_model, device="cuda")).to(torch.bfloat16).requires_grad_(True)
+        w = (torch.randn(d_model, d_model, device="cuda") * d_model ** -0.5).to(torch.bfloat16).requires_grad_(True)
+        bias = torch.zeros(d_model, device="cuda", dtype=torch.bfloat16, requires_grad=True)
+        dy = torch.randn(m, d_model, device="cuda").to(torch.bfloat16)
+        h, xr = native_tf.layer_norm_res(x, g, b, 1e-5)
+        out = native_tf.linear_tc(h, w, bias, residual=xr)
+        out.backward(dy)
+        xf, gf, bf_, wf, biasf = (t.detach().float().requires_grad_(True) for t in (x, g, b, w, bias))
+        ref = torch.nn.functional.layer_norm(xf, (d_model,), gf, bf_, 1e-5) @ wf.t() + biasf + xf
+        ref.backward(dy.float())
+        assert _rel(out, ref) < 1e-2
+        for name, a, r in (("dx", x.grad, xf.grad), ("dgamma", g.grad, gf.grad), ("dbeta", b.grad, bf_.grad),
+                           ("dbias", bias.grad, biasf.grad)):
+            assert _rel(a, r) < 2e-2, (name, _rel(a, r))
