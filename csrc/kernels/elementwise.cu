@@ -96,27 +96,61 @@ __global__ void __launch_bounds__(256) colsum_bf16_acc_kernel(const __nv_bfloat1
 __global__ void __launch_bounds__(256) colsum_bf16_fused_kernel(const __nv_bfloat16* __restrict__ a, __nv_bfloat16* __restrict__ out,
                                                                 float* __restrict__ acc, unsigned* __restrict__ ticket, int M,
                                                                 int N, int rows_per_block) {
-  const int n = blockIdx.x * 64 + (threadIdx.x & 31) * 2;
-  const int r0 = blockIdx.y * rows_per_block + (threadIdx.x >> 5);
+  // block = 256 columns x rows_per_block rows; a lane reads 8 adjacent columns (16 bytes) per row, a warp takes every
+  // 8th row, four rows in flight per lane
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int n = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * rows_per_block + w;
   const int r1 = min(M, (blockIdx.y + 1) * rows_per_block);
-  __shared__ float sh[8][64];
+  __shared__ float sh[8][256];
   __shared__ unsigned last_s;
-  float s0 = 0.f, s1 = 0.f;
-  if (n + 1 < N) {
-    for (int m = r0; m < r1; m += 8) {
-      const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(a + (size_t)m * N + n);
-      s0 += __bfloat162float(v.x);
-      s1 += __bfloat162float(v.y);
-    }
-  }
-  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2] = s0;
-  sh[threadIdx.x >> 5][(threadIdx.x & 31) * 2 + 1] = s1;
-  __syncthreads();
-  if (threadIdx.x < 64 && blockIdx.x * 64 + threadIdx.x < N) {
-    float tot = 0.f;
+  float s[8];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) tot += sh[r][threadIdx.x];
-    atomicAdd(acc + blockIdx.x * 64 + threadIdx.x, tot);
+  for (int e = 0; e < 8; ++e) s[e] = 0.f;
+  if (n + 7 < N) {
+    int m = r0;
+    for (; m + 24 < r1; m += 32) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(a + (size_t)(m + 8 * u) * N + n);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h[e]);
+          s[2 * e] += f.x;
+          s[2 * e + 1] += f.y;
+        }
+      }
+    }
+    for (; m < r1; m += 8) {
+      const uint4 v = *reinterpret_cast<const uint4*>(a + (size_t)m * N + n);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        s[2 * e] += f.x;
+        s[2 * e + 1] += f.y;
+      }
+    }
+  } else {
+    for (int m = r0; m < r1; m += 8)
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (n + e < N) s[e] += __bfloat162float(a[(size_t)m * N + n + e]);
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) sh[w][lane * 8 + e] = s[e];
+  __syncthreads();
+  {
+    const int c = threadIdx.x;
+    if (blockIdx.x * 256 + c < N) {
+      float tot = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) tot += sh[r][c];
+      atomicAdd(acc + blockIdx.x * 256 + c, tot);
+    }
   }
   __threadfence();
   __syncthreads();
@@ -124,9 +158,21 @@ __global__ void __launch_bounds__(256) colsum_bf16_fused_kernel(const __nv_bfloa
   __syncthreads();
   if (last_s) {
     __threadfence();
-    for (int j = threadIdx.x; j < N; j += 256) {
-      out[j] = __float2bfloat16_rn(__ldcg(acc + j));
-      acc[j] = 0.f;
+    for (int j0 = 0; j0 < N; j0 += 256 * 8) {              // eight independent L2 loads in flight per thread
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = j0 + u * 256 + threadIdx.x;
+        v[u] = j < N ? __ldcg(acc + j) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = j0 + u * 256 + threadIdx.x;
+        if (j < N) {
+          out[j] = __float2bfloat16_rn(v[u]);
+          acc[j] = 0.f;
+        }
+      }
     }
     if (threadIdx.x == 0) *ticket = 0u;
   }
@@ -198,9 +244,11 @@ B200_API int b200_colsum_bf16_acc(const void* a, float* acc, int M, int N, cudaS
 
 // acc: fp32 [>= N], ticket: one word; both zero on entry, left zero on exit.  N must be even.
 B200_API int b200_colsum_bf16_fused(const void* a, void* out, float* acc, unsigned* ticket, int M, int N, cudaStream_t stream) {
-  if (N % 2) return static_cast<int>(cudaErrorInvalidValue);
-  const int rows_per_block = 256;
-  dim3 grid(ceil_div(N, 64), ceil_div(M, rows_per_block));
+  if (N % 8 || (reinterpret_cast<uintptr_t>(a) & 15)) return static_cast<int>(cudaErrorInvalidValue);
+  const int col_blocks = ceil_div(N, 256);
+  int rows_per_block = 256;
+  while (rows_per_block > 32 && col_blocks * ceil_div(M, rows_per_block) < 2 * kNumSMs) rows_per_block >>= 1;
+  dim3 grid(col_blocks, ceil_div(M, rows_per_block));
   colsum_bf16_fused_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(a), static_cast<__nv_bfloat16*>(out), acc,
                                                      ticket, M, N, rows_per_block);
   B200_LAUNCH_CHECK();

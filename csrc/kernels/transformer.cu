@@ -144,85 +144,110 @@ layernorm_bwd_bf16_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloa
   __shared__ float gs[D];
   __shared__ unsigned last_s;
   for (int j = threadIdx.x; j < 2 * D; j += 256) sh[j] = 0.f;
-  for (int j = threadIdx.x; j < D; j += 256) gs[j] = __bfloat162float(gamma[j]);
+  // gamma is kept "lane-major" (column v*256 + l*8 + e at gs[(v*8 + e)*32 + l]) so that the 32 lanes of a warp,
+  // which read the same (v, e) of their own 8-column groups, hit 32 different banks
+  for (int j = threadIdx.x; j < D; j += 256) gs[((j >> 8) * 8 + (j & 7)) * 32 + ((j >> 3) & 31)] = __bfloat162float(gamma[j]);
   __syncthreads();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   float pg[NV * 8], pb[NV * 8];
 #pragma unroll
   for (int i = 0; i < NV * 8; ++i) pg[i] = pb[i] = 0.f;
   const float inv_d = 1.f / (float)D;
-  for (int row = blockIdx.x * 8 + w; row < M; row += gridDim.x * 8) {
-    uint4 xv[NV], dv[NV];
-    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
-    const uint4* gr = reinterpret_cast<const uint4*>(dy + (size_t)row * D);
+  // two rows per iteration: all loads of both rows are issued before anything is consumed, which doubles the bytes in
+  // flight per warp (the kernel is latency bound otherwise: 8 warps per SM, one 4 KB row each)
+  const int stride = gridDim.x * 8;
+  for (int row0 = blockIdx.x * 8 + w; row0 < M; row0 += 2 * stride) {
+    uint4 xv[2][NV], dv[2][NV], rv[2][NV];
+    float mu[2], rs[2];
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      xv[v] = xr[v * 32 + lane];
-      dv[v] = gr[v * 32 + lane];
-    }
-    const float mu = mean[row], rs = rstd[row];
-    float a = 0.f, b = 0.f;
+    for (int u = 0; u < 2; ++u) {
+      const int row = row0 + u * stride;
+      if (row < M) {
+        const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * D);
+        const uint4* gr = reinterpret_cast<const uint4*>(dy + (size_t)row * D);
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[v]);
-      const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[v]);
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]);
-        const int c = v * 256 + lane * 8 + 2 * e;
-        const float g0 = df.x * gs[c], g1 = df.y * gs[c + 1];
-        a += g0 + g1;
-        b += g0 * ((xf.x - mu) * rs) + g1 * ((xf.y - mu) * rs);
+        for (int v = 0; v < NV; ++v) {
+          xv[u][v] = xr[v * 32 + lane];
+          dv[u][v] = gr[v * 32 + lane];
+          rv[u][v] = dres ? reinterpret_cast<const uint4*>(dres + (size_t)row * D)[v * 32 + lane] : make_uint4(0, 0, 0, 0);
+        }
+        mu[u] = mean[row];
+        rs[u] = rstd[row];
       }
     }
-    a = warp_sum(a) * inv_d;
-    b = warp_sum(b) * inv_d;
-    uint4* dr = reinterpret_cast<uint4*>(dx + (size_t)row * D);
-    const uint4* rr = dres ? reinterpret_cast<const uint4*>(dres + (size_t)row * D) : nullptr;
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-      const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[v]);
-      const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[v]);
-      uint4 rv = make_uint4(0, 0, 0, 0);
-      if (rr) rv = rr[v * 32 + lane];
-      const __nv_bfloat162* rh2 = reinterpret_cast<const __nv_bfloat162*>(&rv);
-      uint32_t o[4];
+    for (int u = 0; u < 2; ++u) {
+      const int row = row0 + u * stride;
+      if (row >= M) break;
+      float a = 0.f, b = 0.f;
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]), rf = __bfloat1622float2(rh2[e]);
-        const int c = v * 256 + lane * 8 + 2 * e;
-        const float h0 = (xf.x - mu) * rs, h1 = (xf.y - mu) * rs;
-        const float o0 = rs * (df.x * gs[c] - a - h0 * b) + rf.x;
-        const float o1 = rs * (df.y * gs[c + 1] - a - h1 * b) + rf.y;
-        pg[v * 8 + 2 * e] += df.x * h0;
-        pg[v * 8 + 2 * e + 1] += df.y * h1;
-        pb[v * 8 + 2 * e] += df.x;
-        pb[v * 8 + 2 * e + 1] += df.y;
-        const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
-        o[e] = *reinterpret_cast<const uint32_t*>(&ob);
+      for (int v = 0; v < NV; ++v) {
+        const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[u][v]);
+        const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[u][v]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]);
+          const float g0 = df.x * gs[(v * 8 + 2 * e) * 32 + lane], g1 = df.y * gs[(v * 8 + 2 * e + 1) * 32 + lane];
+          a += g0 + g1;
+          b += g0 * ((xf.x - mu[u]) * rs[u]) + g1 * ((xf.y - mu[u]) * rs[u]);
+        }
       }
-      dr[v * 32 + lane] = make_uint4(o[0], o[1], o[2], o[3]);
+      a = warp_sum(a) * inv_d;
+      b = warp_sum(b) * inv_d;
+      uint4* dr = reinterpret_cast<uint4*>(dx + (size_t)row * D);
+#pragma unroll
+      for (int v = 0; v < NV; ++v) {
+        const __nv_bfloat162* xh2 = reinterpret_cast<const __nv_bfloat162*>(&xv[u][v]);
+        const __nv_bfloat162* dh2 = reinterpret_cast<const __nv_bfloat162*>(&dv[u][v]);
+        const __nv_bfloat162* rh2 = reinterpret_cast<const __nv_bfloat162*>(&rv[u][v]);
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 xf = __bfloat1622float2(xh2[e]), df = __bfloat1622float2(dh2[e]), rf = __bfloat1622float2(rh2[e]);
+          const float h0 = (xf.x - mu[u]) * rs[u], h1 = (xf.y - mu[u]) * rs[u];
+          const float o0 = rs[u] * (df.x * gs[(v * 8 + 2 * e) * 32 + lane] - a - h0 * b) + rf.x;
+          const float o1 = rs[u] * (df.y * gs[(v * 8 + 2 * e + 1) * 32 + lane] - a - h1 * b) + rf.y;
+          pg[v * 8 + 2 * e] += df.x * h0;
+          pg[v * 8 + 2 * e + 1] += df.y * h1;
+          pb[v * 8 + 2 * e] += df.x;
+          pb[v * 8 + 2 * e + 1] += df.y;
+          const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
+          o[e] = *reinterpret_cast<const uint32_t*>(&ob);
+        }
+        dr[v * 32 + lane] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
     }
   }
 #pragma unroll
   for (int v = 0; v < NV; ++v)
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int c = v * 256 + lane * 8 + e;
-      atomicAdd(&sh[c], pg[v * 8 + e]);
-      atomicAdd(&sh[D + c], pb[v * 8 + e]);
+      atomicAdd(&sh[(v * 8 + e) * 32 + lane], pg[v * 8 + e]);          // lane-major like gs: conflict-free
+      atomicAdd(&sh[D + (v * 8 + e) * 32 + lane], pb[v * 8 + e]);
     }
   __syncthreads();
-  for (int j = threadIdx.x; j < 2 * D; j += 256) atomicAdd(acc + j, sh[j]);
+  for (int j = threadIdx.x; j < D; j += 256) {               // back to column order for the global accumulator
+    const int t2 = ((j >> 8) * 8 + (j & 7)) * 32 + ((j >> 3) & 31);
+    atomicAdd(acc + j, sh[t2]);
+    atomicAdd(acc + D + j, sh[D + t2]);
+  }
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) last_s = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
   __syncthreads();
   if (last_s) {                                            // every block's additions are visible: finish up
     __threadfence();
-    for (int j = threadIdx.x; j < D; j += 256) {
-      dgamma[j] = __float2bfloat16_rn(__ldcg(acc + j));
-      dbeta[j] = __float2bfloat16_rn(__ldcg(acc + D + j));
+    float vg[NV], vb[NV];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {                           // all loads first: one L2 round trip, not NV
+      vg[v] = __ldcg(acc + v * 256 + threadIdx.x);
+      vb[v] = __ldcg(acc + D + v * 256 + threadIdx.x);
+    }
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+      const int j = v * 256 + threadIdx.x;
+      dgamma[j] = __float2bfloat16_rn(vg[v]);
+      dbeta[j] = __float2bfloat16_rn(vb[v]);
       acc[j] = 0.f;
       acc[D + j] = 0.f;
     }

@@ -67,7 +67,7 @@ def _bias_grad(dy2, param, slot):
     m, n = dy2.shape
     db, _ = _grad_target(param, slot, param)
     sc = scratch(dy2.device)
-    if _bf(dy2) and db.dtype == torch.bfloat16 and m >= 1024 and n % 2 == 0 and n <= sc.red_acc.numel() and db.is_contiguous():
+    if _bf(dy2) and db.dtype == torch.bfloat16 and m >= 1024 and n % 8 == 0 and n <= sc.red_acc.numel() and db.is_contiguous():
         _call("b200_colsum_bf16_fused", _ptr(dy2), _ptr(db), _ptr(sc.red_acc), _ptr(sc.red_ticket), _i(m), _i(n), _stream())
         return db
     if _bf(dy2) and m >= 1024 and n % 2 == 0:
