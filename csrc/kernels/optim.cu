@@ -50,7 +50,32 @@ __global__ void __launch_bounds__(256) sgd_kernel(const TensorRec* __restrict__ 
     }
     return fmaf(-lr, g, p);
   };
-  if (r.dtype == 1) {
+  if (r.dtype == 1 && vec && (end - base) % 8 == 0 && base % 8 == 0) {
+    // bf16 parameters / gradients, 8 per thread (16-byte loads and stores), fp32 momentum
+    __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(r.p);
+    const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(r.g);
+    for (long long i = base + threadIdx.x * 8; i < end; i += 256 * 8) {
+      uint4 pv = *reinterpret_cast<const uint4*>(pb + i);
+      const uint4 gv = *reinterpret_cast<const uint4*>(gb + i);
+      float b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (r.s0) {
+        const float4 b0 = *reinterpret_cast<const float4*>(r.s0 + i), b1 = *reinterpret_cast<const float4*>(r.s0 + i + 4);
+        b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+      }
+      __nv_bfloat162* p2 = reinterpret_cast<__nv_bfloat162*>(&pv);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 pf = __bfloat1622float2(p2[e]), gf = __bfloat1622float2(g2[e]);
+        p2[e] = __floats2bfloat162_rn(upd(pf.x, gf.x, b[2 * e]), upd(pf.y, gf.y, b[2 * e + 1]));
+      }
+      *reinterpret_cast<uint4*>(pb + i) = pv;
+      if (r.s0) {
+        *reinterpret_cast<float4*>(r.s0 + i) = make_float4(b[0], b[1], b[2], b[3]);
+        *reinterpret_cast<float4*>(r.s0 + i + 4) = make_float4(b[4], b[5], b[6], b[7]);
+      }
+    }
+  } else if (r.dtype == 1) {
     __nv_bfloat16* pb = reinterpret_cast<__nv_bfloat16*>(r.p);
     const __nv_bfloat16* gb = reinterpret_cast<const __nv_bfloat16*>(r.g);
     for (long long i = base + threadIdx.x; i < end; i += 256) {

@@ -196,6 +196,32 @@ def test_fused_sgd_matches_torch(nat, momentum, wd, nesterov):
     assert a.state_dict()["param_groups"][0].keys() == b.state_dict()["param_groups"][0].keys()
 
 
+@pytest.mark.parametrize("momentum", [0.0, 0.9])
+def test_fused_sgd_bf16_parameters(nat, momentum):
+    """bf16 parameters / gradients (vectorised path for 8-element-aligned tensors, scalar path otherwise) against
+    the same update computed in fp32 on the bf16-rounded values; momentum state is fp32."""
+    import distributeddataparallel_b200 as d
+
+    torch.manual_seed(1)
+    shapes = [(1024, 1024), (4096,), (50257, 16), (77,), (3, 5)]
+    ps = [torch.randn(s, device="cuda").to(torch.bfloat16).requires_grad_(True) for s in shapes]
+    ref = [p.detach().float() for p in ps]
+    bufs = [torch.zeros_like(r) for r in ref]
+    opt = d.SGD(ps, lr=0.05, momentum=momentum)
+    for it in range(3):
+        for p, r, b in zip(ps, ref, bufs):
+            g = torch.randn_like(p)
+            p.grad = g
+            gf = g.float()
+            if momentum:
+                b.copy_(gf if it == 0 else momentum * b + gf)
+                gf = b
+            r.copy_((r - 0.05 * gf).to(torch.bfloat16).float())
+        opt.step()
+    for p, r in zip(ps, ref):
+        assert torch.allclose(p.float(), r, rtol=1e-2, atol=1e-2), (p.shape, (p.float() - r).abs().max())
+
+
 def test_fused_adam_matches_torch(nat):
     import distributeddataparallel_b200 as d
 
