@@ -118,7 +118,10 @@ struct Args {
   // batched GEMM (attention): blockIdx.z = batch index z, element offsets (z / inner) * s0 + (z % inner) * s1
   int batch, inner;
   long long a_s0, a_s1, b_s0, b_s1, o_s0, o_s1;
-  int tma_a, tma_b;            // operand is fetched by TMA (dense operands of non-batched calls)
+  int tma_a, tma_b;            // operand is fetched by TMA: 1 tiled, 2 im2col (K-major), 3 fp32 MN-major tiled,
+                               // 4 im2col fp32 MN-major (wgrad), 5 filter as {C, RS, K} boxes with flipped taps (dgrad)
+  const void* filter3d;        // != nullptr: WEIGHT_T_MN operand is the original KRSC filter, fetched by mode 5
+  int filter_k;                // its K (number of filters); its C is the tile's mn extent
   PeerReduce peer;             // world > 1: fused all-reduce epilogue (needs splits == 1, row-major out)
   // causal attention structure (batched calls): 1 = output tile is entirely above the diagonal -> skip it
   // (S = QK^T, dP = dO V^T); 2 = reduction index is the key, only keys <= query row matter (P V, dS K);
@@ -401,10 +404,17 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         const int k0 = k_begin + kb * KELEMS;
         if (t == 0 && tx_bytes) {
           mbar_expect_tx(&full_bar[s], tx_bytes);
-          if (a.tma_a == 2 || a.tma_b == 2) {              // k-block -> (filter tap, first channel)
+          if (a.tma_a == 2 || a.tma_b == 2 || a.tma_a == 5 || a.tma_b == 5) {   // k-block -> (filter tap, first channel)
             int rs, c0, r, sx;
             a.g.fC.divmod(k0, rs, c0);
             a.g.fS.divmod(rs, r, sx);
+            // dgrad as a forward convolution of dY: the filter tap that meets window offset (r, s) is the mirrored one,
+            // and the reduction "channel" c0 is the filter index k'
+            const int rs_flip = a.g.R * a.g.S - 1 - rs;
+            if (a.tma_a == 5)
+              for (int bx = 0; bx < BM / 32; ++bx) tma_load_3d(smem_a + s * A_STAGE + bx * 4096, &map_a, m0 + bx * 32, rs_flip, c0, &full_bar[s]);
+            if (a.tma_b == 5)
+              for (int bx = 0; bx < BN / 32; ++bx) tma_load_3d(smem_b + s * B_STAGE + bx * 4096, &map_b, n0 + bx * 32, rs_flip, c0, &full_bar[s]);
             if (a.tma_a == 2)
               tma_load_im2col_4d(smem_a + s * A_STAGE, &map_a, c0, im_w_a, im_h_a, im_n_a, (unsigned short)sx, (unsigned short)r, &full_bar[s]);
             if (a.tma_b == 2)
@@ -485,7 +495,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
         // a TMA-fetched bf16 MN-major operand sits in the SWIZZLE_128B MN-major layout instead:
         // 64-mn atoms 8 KB apart (LBO), 8-k-row atoms 1 KB apart (SBO), 2 k-atoms per MMA
         const bool a_mn_tma = is_mn(AK) && a.tma_a == 1, b_mn_tma = is_mn(BK_) && a.tma_b == 1;
-        const uint64_t da = a.tma_a == 3 ? make_desc(smem_a + s * A_STAGE + j * 1024, 4096, 512, 1u)
+        const uint64_t da = a.tma_a >= 3 ? make_desc(smem_a + s * A_STAGE + j * 1024, 4096, 512, 1u)
                           : a_mn_tma ? make_desc(smem_a + s * A_STAGE + j * 2048, 8192, 1024, 2u)
                                      : make_desc(smem_a + s * A_STAGE + j * A_STEP, A_LBO, A_SBO, A_TYPE);
         const uint64_t db = a.tma_b >= 3 ? make_desc(smem_b + s * B_STAGE + j * 1024, 4096, 512, 1u)
@@ -1169,6 +1179,7 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inne
 static bool g_use_tma = true;
 static int g_split_cap = 32;          // upper bound on the split-K factor (per-shape tuning knob, see ops/native.py)
 static bool g_use_im2col_tma = true;
+static bool g_use_filter3d = true;    // stride-1 dgrad reads the KRSC filter through a 3-D TMA descriptor (no re-layout kernel)
 static bool g_use_mn32_tma = true;    // fp32 MN-major operands by TMA (SWIZZLE_128B_ATOM_32B)
 static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom& g, int channels, int pixels) {
   return tma_make_map_im2col(m, x, bf16, g.Nb, g.H, g.W, g.C, g.R, g.S, g.P, g.Q, g.stride, g.pad, channels, pixels);
@@ -1191,6 +1202,11 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     else if (BK_ == DENSE_MN && BF16 && BN >= 64) a.tma_b = make_map(&map_b, a.b, true, a.N, a.Kd, a.ldb, 64, KELEMS);
     else if (BK_ == DENSE_MN && !BF16 && g_use_mn32_tma &&
              tma_make_map_2d(&map_b, a.b, false, a.N, a.Kd, a.ldb, 32, KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) a.tma_b = 3;
+    if (!BF16 && a.filter3d != nullptr) {                   // required: the gather code cannot serve this operand
+      const int rs = a.g.R * a.g.S;
+      if (AK == WEIGHT_T_MN) { if (!tma_make_map_filter_3d(&map_a, a.filter3d, a.filter_k, rs, a.M)) return 801; a.tma_a = 5; }
+      if (BK_ == WEIGHT_T_MN) { if (!tma_make_map_filter_3d(&map_b, a.filter3d, a.filter_k, rs, a.N)) return 801; a.tma_b = 5; }
+    }
     if (BK_ == IM2COL_MN && !BF16 && g_use_im2col_tma && g_use_mn32_tma && a.g.C % 32 == 0 &&
         tma_make_map_im2col(&map_b, a.b, false, a.g.Nb, a.g.H, a.g.W, a.g.C, a.g.R, a.g.S, a.g.P, a.g.Q, a.g.stride, a.g.pad, 32,
                             KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
@@ -1201,6 +1217,7 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
       if (BK_ == IM2COL_K && make_im2col_map(&map_b, a.b, BF16, a.g, KELEMS, BN)) a.tma_b = 2;
     }
   }
+  if (a.filter3d != nullptr && !((a.tma_a == 5 && a.tma_b == 2) || (a.tma_a == 2 && a.tma_b == 5))) return 801;
   static bool configured = false;     // per template instantiation
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_kernel<AK, BK_, BN, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -1331,6 +1348,7 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 // 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_use_filter3d(int enabled) { b200::tc::g_use_filter3d = enabled != 0; }
 B200_API void b200_gemm_tc_use_mn32_tma(int enabled) { b200::tc::g_use_mn32_tma = enabled != 0; }
 B200_API void b200_gemm_tc_split_cap(int cap) { b200::tc::g_split_cap = cap < 1 ? 1 : cap; }
 B200_API void b200_gemm_tc_use_im2col_tma(int enabled) { b200::tc::g_use_im2col_tma = enabled != 0; }
@@ -1453,6 +1471,23 @@ B200_API int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, in
   // Stride-1 filters: dX is itself a convolution of dY (padding R-1-pad) with the flipped, transposed filter.
   // The filter is re-laid-out into the tail of the workspace (a few MB at most), after which the forward kernels
   // -- im2col-mode TMA for dY, tiled TMA for the filter -- do the work; no gather code runs on the SMs.
+  if (!pointwise && g_use_im2col_tma && g_use_mn32_tma && g_use_tma && g_use_filter3d && stride == 1 && R == S &&
+      R - 1 - pad >= 0 && K % 32 == 0 && C % 4 == 0) {
+    // no re-layout at all: the original KRSC filter is fetched as {32 c, mirrored tap, 32 k'} boxes (MN-major operand)
+    Args f{};
+    f.g = make_geom(Nb, a.g.P, a.g.Q, K, C, R, S, 1, R - 1 - pad);
+    f.Kd = R * S * K; f.workspace = workspace; f.counters = counters; f.error = error; f.out = dx; f.ldo = C;
+    f.filter3d = w; f.filter_k = K;
+    int rc;
+    if (pixels >= 1024 || C < 128) {
+      f.a = dy; f.b = w; f.lda = K; f.ldb = C; f.M = pixels; f.N = C;
+      rc = dispatch_bn<IM2COL_K, WEIGHT_T_MN, false>(f, workspace_bytes, max_counters, 0, stream);
+    } else {
+      f.a = w; f.b = dy; f.lda = C; f.ldb = K; f.M = C; f.N = pixels; f.transpose_out = 1;
+      rc = dispatch_bn<WEIGHT_T_MN, IM2COL_K, false>(f, workspace_bytes, max_counters, 0, stream);
+    }
+    if (rc != 801) return rc;
+  }
   const size_t wt_bytes = (size_t)C * R * S * K * sizeof(float);
   if (!pointwise && g_use_im2col_tma && g_use_tma && stride == 1 && R == S && R - 1 - pad >= 0 && K % 32 == 0 && workspace &&
       2 * wt_bytes <= workspace_bytes) {

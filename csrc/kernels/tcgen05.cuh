@@ -74,6 +74,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 
+// 3-D tiled TMA load (c0 innermost)
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+
 // 4-D im2col-mode TMA load (NHWC activations): box = pixels_per_column pixels x channels_per_pixel channels,
 // starting at base pixel (w, h, n) -- input-space coordinates of the filter window's corner, may be negative
 // inside the padding -- shifted by the filter tap (off_w, off_h); rows land like a tiled load (128 B, swizzled).
@@ -176,6 +183,24 @@ static inline bool tma_make_map_2d(CUtensorMap* m, const void* base, bool bf16, 
   if (rc != CUDA_SUCCESS && getenv("B200DDP_DEBUG_TMA"))
     fprintf(stderr, "cuTensorMapEncodeTiled rc=%d base=%p inner=%lld outer=%lld pitch=%lld box=%dx%d\n", (int)rc, base, inner,
             outer, pitch_elems, box_inner, box_outer);
+  return rc == CUDA_SUCCESS;
+}
+
+// fp32 KRSC filter [K][R*S][C] as a 3-D tensor {C, RS, K}: a box {32 channels, one tap, 32 filters} lands as 32 rows
+// (filters) of 128 bytes (channels) in the SWIZZLE_128B_ATOM_32B pattern = an MN-major fp32 UMMA operand block.
+static inline bool tma_make_map_filter_3d(CUtensorMap* m, const void* w, int K, int RS, int C) {
+  TmaEncodeTiledFn fn = tma_encode_fn();
+  if (!fn) return false;
+  cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)RS, (cuuint64_t)K};
+  cuuint64_t strides[2] = {(cuuint64_t)C * 4, (cuuint64_t)RS * C * 4};
+  cuuint32_t box[3] = {32, 1, 32};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult rc = CUDA_SUCCESS;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    rc = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_ERROR_INVALID_CONTEXT || cudaFree(nullptr) != cudaSuccess) break;
+  }
   return rc == CUDA_SUCCESS;
 }
 
