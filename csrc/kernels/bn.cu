@@ -62,7 +62,28 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(
   const float inv_m = 1.f / (float)M;
   const size_t total4 = (size_t)M * C / 4;
   const int c4n = C >> 2;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+  // the LAST block only does the per-channel bookkeeping (saved statistics, running statistics, clearing the other
+  // accumulator), concurrently with the blocks that normalise: its dependent L2 round trips no longer extend the kernel
+  const unsigned work_blocks = gridDim.x - 1;
+  if (blockIdx.x == work_blocks) {
+    if (training) {
+      for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float m = sums[c] * inv_m;
+        const float var = fmaxf(sums[C + c] * inv_m - m * m, 0.f);
+        save_mean[c] = m;
+        save_invstd[c] = rsqrtf(var + eps);
+        if (running_mean != nullptr) {
+          const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+          running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
+          running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+        }
+      }
+      if (threadIdx.x == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
+    }
+    for (int i = threadIdx.x; i < zero_count; i += blockDim.x) zero_after[i] = 0.f;
+    return;
+  }
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)work_blocks * blockDim.x) {
     const int c = (int)(i % c4n) * 4;
     float mean[4], istd[4];
 #pragma unroll
@@ -90,23 +111,6 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(
     }
     if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
     st4(out + i * 4, o);
-  }
-  if (blockIdx.x == 0) {
-    if (training) {
-      for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        const float m = sums[c] * inv_m;
-        const float var = fmaxf(sums[C + c] * inv_m - m * m, 0.f);
-        save_mean[c] = m;
-        save_invstd[c] = rsqrtf(var + eps);
-        if (running_mean != nullptr) {
-          const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
-          running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
-          running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-        }
-      }
-      if (threadIdx.x == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
-    }
-    for (int i = threadIdx.x; i < zero_count; i += blockDim.x) zero_after[i] = 0.f;
   }
 }
 
@@ -321,7 +325,7 @@ B200_API int b200_bn_fwd_apply(const float* x, const float* sums, const float* g
                                float* zero_after, int zero_count, int M, int C, float momentum, float eps,
                                int relu, int training, cudaStream_t stream) {
   if (C % 4 != 0) return static_cast<int>(cudaErrorInvalidValue);
-  const int grid = grid_for((size_t)M * C / 4, 256 * 2, 4 * kNumSMs);
+  const int grid = grid_for((size_t)M * C / 4, 256 * 2, 4 * kNumSMs) + 1;      // + the bookkeeping block
   bn_fwd_apply_kernel<<<grid, 256, 0, stream>>>(x, sums, gamma, beta, residual, out, running_mean, running_var,
                                                 num_batches_tracked, save_mean, save_invstd, zero_after, zero_count,
                                                 M, C, momentum, eps, relu, training);
@@ -334,7 +338,7 @@ B200_API int b200_bn_bwd_reduce(const float* dy, const float* out, const float* 
   if (C % 4 != 0) return static_cast<int>(cudaErrorInvalidValue);
   const int chunks = ceil_div(C / 4, 256);
   const int rows_per_block = max(1, 256 / min(C / 4, 256));
-  const int gx = grid_for((size_t)M, rows_per_block * 4, max(1, 2 * kNumSMs / chunks));
+  const int gx = grid_for((size_t)M, rows_per_block * 2, max(1, 4 * kNumSMs / chunks));   // <= 2 rows per thread
   bn_bwd_reduce_kernel<<<dim3(gx, chunks), 256, 0, stream>>>(dy, out, x, save_mean, save_invstd, sums, M, C, relu);
   B200_LAUNCH_CHECK();
 }
