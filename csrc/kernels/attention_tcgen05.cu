@@ -84,6 +84,7 @@ attn_fwd_kernel(const FwdArgs a, const __grid_constant__ CUtensorMap map_qkv) {
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = base, sRing = base + TILE_BYTES, sP = base + 4 * TILE_BYTES;
 
+  if (t == 32) tma_prefetch_desc(&map_qkv);
   if (t == 0) {
     mbar_init(&q_full, 1);
     for (int s = 0; s < 3; ++s) {
@@ -276,6 +277,10 @@ attn_bwd_kernel(const BwdArgs a, const __grid_constant__ CUtensorMap map_qkv, co
   const uint32_t sQ0 = base + 2 * TILE_BYTES;              // stage st: Q at sQ0 + st*2*TILE, dO right after it
   const uint32_t sP = base + 6 * TILE_BYTES, sdS = base + 8 * TILE_BYTES;
 
+  if (t == 32) {
+    tma_prefetch_desc(&map_qkv);
+    tma_prefetch_desc(&map_do);
+  }
   if (t == 0) {
     mbar_init(&kv_full, 1);
     for (int s = 0; s < 2; ++s) {

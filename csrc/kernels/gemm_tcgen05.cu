@@ -350,6 +350,10 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   const int num_kb = (k_end - k_begin + KELEMS - 1) / KELEMS;
   const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + STAGES * A_STAGE;   // swizzle is address based
 
+  if (t == 32) {
+    if (a.tma_a) tma_prefetch_desc(&map_a);
+    if (a.tma_b) tma_prefetch_desc(&map_b);
+  }
   if (t == 0) {
     for (int s = 0; s < STAGES; ++s) {
       // arrivals per stage: the 256 gather threads (if any operand is gathered) + the TMA issuer
@@ -998,6 +1002,10 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
   const int num_kb = (a.Kd + KELEMS - 1) / KELEMS;
   const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + ST * A_STAGE;
 
+  if (t == 96) {
+    tma_prefetch_desc(&map_a);
+    tma_prefetch_desc(&map_b);
+  }
   if (t == 0) {
     for (int s = 0; s < ST; ++s) {
       mbar_init(&full_bar[s], 1);

@@ -74,6 +74,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
 
+// Start fetching a TMA descriptor (kernel parameter) into the descriptor cache: issued by one thread at kernel
+// entry so the ~0.5 us fetch overlaps barrier initialisation and TMEM allocation instead of the first load.
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
 // 3-D tiled TMA load (c0 innermost)
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
   asm volatile(
