@@ -107,6 +107,7 @@ struct Args {
   int M, N, Kd;
   Geom g;
   int splits, k_per_split;     // k_per_split in elements, multiple of the stage depth
+  int cluster_reduce;          // the splits of a tile form one thread-block cluster and reduce through distributed smem
   float* workspace;
   unsigned* counters;
   const float* bias;           // per output CHANNEL (column, or row when transposed)
@@ -329,7 +330,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   constexpr int A_STAGE = BM * ROW_BYTES, B_STAGE = BN * ROW_BYTES;
   constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;          // 32 / 64 / 128 / 256: powers of two
   extern __shared__ __align__(1024) unsigned char smem[];
-  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar;
+  __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar, cl_ready, cl_done;
   __shared__ uint32_t tmem_base_s;
   __shared__ unsigned ticket_s;
 
@@ -361,11 +362,16 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(&accum_bar, 1);
+    if (a.cluster_reduce) {
+      mbar_init(&cl_ready, a.splits);
+      mbar_init(&cl_done, a.splits);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 8) tmem_alloc(&tmem_base_s, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
+  if (a.cluster_reduce) cluster_sync_all();                 // every CTA's cl_* barriers exist before anyone signals them
   tc_fence_after();
   const uint32_t tmem_d = tmem_base_s;
 
@@ -527,7 +533,90 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
     // the accumulator is streamed out of TMEM 16 columns at a time (keeps the epilogue at 16 live
     // accumulator registers even for 256-column tiles)
     const uint32_t tmem_row = tmem_d + ((uint32_t)(lane_grp * 32) << 16) + (uint32_t)col_base;
-    if (a.splits > 1) {
+    if (a.splits > 1 && a.cluster_reduce) {
+      // ---- split-K inside a thread-block cluster: partial tiles stay in shared memory; every split CTA sums its
+      // slice of rows straight out of its peers' shared memory (DSMEM) -- no workspace round trip through L2, no
+      // global fence, no ticket spin.
+      constexpr int LDS = BN + 1;
+      float* stage = reinterpret_cast<float*>(smem + (smem_a - smem_u32(smem)));      // my partial [BM][LDS]
+      float* red = stage + BM * LDS;                                                 // my reduced slice [<= 64][LDS]
+#pragma unroll 1
+      for (int c = 0; c < NCH; ++c) {
+        float acc[16];
+        tmem_ld16(tmem_row + c * 16, acc);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) stage[row * LDS + col_base + c * 16 + j] = acc[j];
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (t < a.splits) mbar_arrive_release_cluster(map_to_cta(smem_u32(&cl_ready), (uint32_t)t));
+      mbar_wait_cluster(&cl_ready, 0, a.error);
+      const int rows_per = (BM + a.splits - 1) / a.splits;
+      const int r0 = split_z * rows_per;
+      const int nrows = max(0, min(BM, r0 + rows_per) - r0);
+      const uint32_t stage_u32 = smem_u32(stage);
+      for (int idx = t; idx < nrows * BN; idx += PRODUCERS) {
+        const int rr = idx / BN, col = idx - rr * BN;             // lanes walk columns: contiguous remote reads
+        const uint32_t local = stage_u32 + (uint32_t)(((r0 + rr) * LDS + col) * 4);
+        float v = 0.f;
+        for (int sp = 0; sp < a.splits; ++sp) v += ld_dsmem_f32(map_to_cta(local, (uint32_t)sp));   // fixed order
+        red[rr * LDS + col] = v;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (t < a.splits) mbar_arrive_release_cluster(map_to_cta(smem_u32(&cl_done), (uint32_t)t));   // done reading peer t
+      const int lane = t & 31;
+      if (!a.transpose_out) {
+        for (int rr = warp; rr < nrows; rr += 8) {
+          const int gr = m0 + r0 + rr;
+          if (gr >= a.M) break;
+          for (int col = lane; col < BN; col += 32) {
+            const int gc = n0 + col;
+            if (gc < a.N) {
+              float v = red[rr * LDS + col];
+              if (a.bias != nullptr) v += load_bias(a, gc);
+              store_out(a, out_base, (size_t)gr * a.ldo + gc, v);
+            }
+          }
+        }
+        if (a.stats != nullptr && t < BN && n0 + t < a.N) {
+          const int rows = min(nrows, a.M - m0 - r0);
+          float cs = 0.f, cq = 0.f;
+          const float bias = a.bias != nullptr ? load_bias(a, n0 + t) : 0.f;
+          for (int rr = 0; rr < rows; ++rr) {
+            const float v = red[rr * LDS + t] + bias;
+            cs += v;
+            cq += v * v;
+          }
+          if (rows > 0) {
+            atomicAdd(a.stats + n0 + t, cs);
+            atomicAdd(a.stats + a.N + n0 + t, cq);
+          }
+        }
+      } else {
+        for (int idx = t; idx < nrows * BN; idx += PRODUCERS) {
+          const int rr = idx % nrows, col = idx / nrows;
+          const int gr = m0 + r0 + rr, gc = n0 + col;
+          if (gr < a.M && gc < a.N) {
+            float v = red[rr * LDS + col];
+            if (a.bias != nullptr) v += load_bias(a, gr);
+            store_out(a, out_base, (size_t)gc * a.ldo + gr, v);
+          }
+        }
+        if (a.stats != nullptr && t < nrows && m0 + r0 + t < a.M) {
+          const int cols = min(BN, a.N - n0);
+          const float bias = a.bias != nullptr ? load_bias(a, m0 + r0 + t) : 0.f;
+          float cs = 0.f, cq = 0.f;
+          for (int col = 0; col < cols; ++col) {
+            const float v = red[t * LDS + col] + bias;
+            cs += v;
+            cq += v * v;
+          }
+          atomicAdd(a.stats + m0 + r0 + t, cs);
+          atomicAdd(a.stats + a.M + m0 + r0 + t, cq);
+        }
+      }
+      mbar_wait_cluster(&cl_done, 0, a.error);               // my shared memory is no longer being read: safe to leave
+      writer = false;
+    } else if (a.splits > 1) {
       // ---- split-K: park the partial tile, then ALL splits of this tile reduce it together ----
       // Every split CTA sums one slice of rows over all parked partials and writes that slice of
       // the output, so the reduction cost per CTA is one tile of reads no matter how many splits
@@ -813,20 +902,6 @@ __global__ void __launch_bounds__(256) peer_reduce_wait_kernel(PeerReduce pr, in
 constexpr int T2_THREADS = 256;      // warp 0: TMA, warp 1: MMA (leader), warp 2: TMEM alloc, warps 4-7: epilogue
 constexpr int T2P_THREADS = 384;     // persistent variant: warps 4-11 are the epilogue (two per TMEM lane quarter)
 
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t cta) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(cta));
-  return r;
-}
 __device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster) {
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
@@ -977,9 +1052,6 @@ gemm2_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __gr
 //   tmem_full[2]     : MMA -> epilogue, multicast commit to both CTAs
 //   tmem_empty[2]    : epilogue -> MMA, lives in the LEADER, 4 warps x 2 CTAs arrive (peer arrives remotely)
 // -----------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
-  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
-}
 
 template <int AK, int BK_, int BN, bool BF16, int ST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2P_THREADS, 1)
@@ -1185,6 +1257,7 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, long long inne
 }
 
 static bool g_use_tma = true;
+static bool g_cluster_reduce = false;  // split-K partials reduced through distributed shared memory (tuner-selected)
 static int g_split_cap = 32;          // upper bound on the split-K factor (per-shape tuning knob, see ops/native.py)
 static bool g_use_im2col_tma = true;
 static bool g_use_filter3d = true;    // stride-1 dgrad reads the KRSC filter through a 3-D TMA descriptor (no re-layout kernel)
@@ -1231,6 +1304,24 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(gemm_kernel<AK, BK_, BN, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
+  }
+  if (a.cluster_reduce) {
+    // the splits of one output tile (grid.z) form a cluster
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 1;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = grid.z;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<AK, BK_, BN, BF16>, a, map_a, map_b);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    return static_cast<int>(cudaPeekAtLastError());
   }
   gemm_kernel<AK, BK_, BN, BF16><<<grid, THREADS, smem, st>>>(a, map_a, map_b);
   return static_cast<int>(cudaPeekAtLastError());
@@ -1335,9 +1426,12 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
     if ((size_t)splits * per_split > workspace_bytes) splits = (int)(workspace_bytes / per_split);
     splits = max(splits, 1);
   }
+  const bool want_cluster = g_cluster_reduce && splits > 1 && bn <= 128 && a.peer.world <= 1;
+  if (want_cluster) splits = min(splits, 8);                // portable cluster size limit
   const int kps = ceil_div(k_blocks, splits) * KELEMS;
   a.splits = ceil_div(a.Kd, kps);
   a.k_per_split = kps;
+  a.cluster_reduce = want_cluster && a.splits > 1 && a.splits <= 8;
   dim3 grid(tm, tn, a.batch > 1 ? a.batch : a.splits);
   if (bn == 32) return launch<AK, BK_, 32, BF16>(a, grid, st);
   if (bn == 64) return launch<AK, BK_, 64, BF16>(a, grid, st);
@@ -1359,6 +1453,7 @@ B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled 
 B200_API void b200_gemm_tc_use_filter3d(int enabled) { b200::tc::g_use_filter3d = enabled != 0; }
 B200_API void b200_gemm_tc_use_mn32_tma(int enabled) { b200::tc::g_use_mn32_tma = enabled != 0; }
 B200_API void b200_gemm_tc_split_cap(int cap) { b200::tc::g_split_cap = cap < 1 ? 1 : cap; }
+B200_API void b200_gemm_tc_cluster_reduce(int enabled) { b200::tc::g_cluster_reduce = enabled != 0; }
 B200_API void b200_gemm_tc_use_im2col_tma(int enabled) { b200::tc::g_use_im2col_tma = enabled != 0; }
 B200_API void b200_gemm_tc_use_2cta(int mode) { b200::tc::g_use_2cta = mode; }   // 0 off, 1 simple, 2 persistent
 

@@ -147,19 +147,30 @@ def conv_choices() -> Dict[tuple, int]:
     return dict(_choice)
 
 
-_SPLIT_CAPS = (32, 1, 4)              # split-K upper bounds the tuner tries for a tcgen05 convolution
+# split-K variants the tuner tries for a tcgen05 convolution: (upper bound on the split factor, reduce the splits
+# through a thread-block cluster's distributed shared memory instead of an L2 workspace); a choice is stored as
+# cap + 100 * cluster
+_TC_VARIANTS = ((32, 0), (1, 0), (4, 0), (12, 0), (8, 1), (4, 1), (2, 1))
+if os.environ.get("B200DDP_TC_VARIANTS"):          # e.g. "32,1,4,108": restrict what the tuner may pick (A/B runs)
+    _TC_VARIANTS = tuple((int(v) % 100, int(v) // 100) for v in os.environ["B200DDP_TC_VARIANTS"].split(","))
+_FORCE_CLUSTER = os.environ.get("B200DDP_CLUSTER_REDUCE", "") == "1"     # testing: cluster reduction wherever K is split
 
 
-def _launch_tc(name, head, geom, dev, cap: int = 32) -> int:
+def _launch_tc(name, head, geom, dev, variant: int = 32) -> int:
     s = scratch(dev)
     lib = load_library()
-    if cap == 32:
+    cap, cluster = variant % 100, variant // 100
+    if _FORCE_CLUSTER and variant == 32:
+        cap, cluster = 8, 1
+    if cap == 32 and not cluster:
         return getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
-    lib.b200_gemm_tc_split_cap(_i(cap))            # library-wide knob: restore it for every other GEMM caller
+    lib.b200_gemm_tc_split_cap(_i(cap))            # library-wide knobs: restore them for every other GEMM caller
+    lib.b200_gemm_tc_cluster_reduce(_i(cluster))
     try:
         return getattr(lib, name + "_tc")(*head, *geom, *_ws_args(dev), _ptr(s.error), _stream())
     finally:
         lib.b200_gemm_tc_split_cap(_i(32))
+        lib.b200_gemm_tc_cluster_reduce(_i(0))
 
 
 def _launch_ffma(name, head, geom, dev) -> int:
@@ -170,18 +181,42 @@ def _launch_ffma(name, head, geom, dev) -> int:
     return getattr(lib, name)(*head, *geom, *_ws_args(dev), _stream())
 
 
-def _time_variant(fn, iters: int = 3) -> float:
+_flush_buf: Dict[int, torch.Tensor] = {}
+
+
+def _time_variant(fn, acts=(), iters: int = 6) -> float:
+    """Device time of one call under the cache state it meets inside a training step: before every launch the L2 is
+    flushed (a 160 MB memset, larger than the 126 MB L2) and the activation operands ``acts`` -- which in a real
+    step were just written by the previous kernel -- are read back in, so filters come from HBM and activations
+    from L2.  The launches are captured in a CUDA graph and replayed (no host launch cost in the measurement); the
+    flush and re-warm cost is the same for every variant, so totals are compared directly."""
     fn()
+    torch.cuda.synchronize()
+    dev = torch.cuda.current_device()
+    buf = _flush_buf.get(dev)
+    if buf is None:
+        buf = _flush_buf[dev] = torch.empty(160 << 20, dtype=torch.uint8, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        for _ in range(iters):
+            buf.zero_()
+            for t in acts:
+                t.sum()
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(iters):
-        fn()
+    g.replay()
+    g.replay()
     e1.record()
     e1.synchronize()
-    return e0.elapsed_time(e1) / iters
+    return e0.elapsed_time(e1) / (2 * iters)
 
 
-def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device) -> None:
+def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device, acts=()) -> None:
     """Dispatch one convolution pass to the tcgen05 kernel (with a tuned split-K bound) or to the FFMA kernel."""
     global _launches, tc_launches, ffma_launches
     choice = 32 if _tc_mode == "1" else 0          # 0 = FFMA, otherwise the split-K cap of the tcgen05 call
@@ -199,11 +234,12 @@ def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device) -> None:
                     quiet = head[:3] + (_i(0),)
                 choice = 0
                 if _launch_tc(name, quiet, geom, dev) == 0:
-                    best = _time_variant(lambda: _launch_ffma(name, quiet, geom, dev), 5)
-                    for cap in _SPLIT_CAPS:
-                        t = _time_variant(lambda: _launch_tc(name, quiet, geom, dev, cap), 5)
+                    best = _time_variant(lambda: _launch_ffma(name, quiet, geom, dev), acts)
+                    for cap, cluster in _TC_VARIANTS:
+                        v = cap + 100 * cluster
+                        t = _time_variant(lambda: _launch_tc(name, quiet, geom, dev, v), acts)
                         if t < best:
-                            best, choice = t, cap
+                            best, choice = t, v
                 _choice[key] = choice
     if choice:
         rc = _launch_tc(name, head, geom, dev, choice)
@@ -311,7 +347,7 @@ class _Conv2d(torch.autograd.Function):
         n, h, wd, c, k, r, s, p, q = _conv_geom(xc, wc, stride, pad)
         y = _empty_nhwc(n, k, p, q, x.device)
         _conv_call("b200_conv2d_fprop", (_ptr(xc), _ptr(wc), _ptr(y), _ptr(stats)),
-                   (_i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad)), x.device)
+                   (_i(n), _i(h), _i(wd), _i(c), _i(k), _i(r), _i(s), _i(stride), _i(pad)), x.device, acts=(xc,))
         ctx.save_for_backward(xc, wc)
         ctx.geom = (n, h, wd, c, k, r, s, stride, pad)
         ctx.param = w
@@ -328,14 +364,14 @@ class _Conv2d(torch.autograd.Function):
         dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = _empty_nhwc(n, c, h, wd, dy.device)
-            _conv_call("b200_conv2d_dgrad", (_ptr(dy), _ptr(wc), _ptr(dx)), geom, dy.device)
+            _conv_call("b200_conv2d_dgrad", (_ptr(dy), _ptr(wc), _ptr(dx)), geom, dy.device, acts=(dy,))
         if ctx.needs_input_grad[1]:
             if ctx.c_real is None:
                 dw, acc = _grad_target(ctx.param, ctx.slot, wc)
-                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device)
+                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device, acts=(dy, xc))
             else:
                 dw_pad = torch.empty_like(wc)
-                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw_pad), _i(0)), geom, dy.device)
+                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw_pad), _i(0)), geom, dy.device, acts=(dy, xc))
                 dw, acc = _grad_target(ctx.param, ctx.slot, _nhwc(ctx.param))
                 if acc:
                     dw.add_(dw_pad[:, :ctx.c_real])

@@ -140,6 +140,7 @@ int b200_gemm_tc_peer(const void* A, const void* B, const void* bias, int M, int
 void b200_gemm_tc_use_tma(int enabled);   /* dense operands via TMA (default) or cp.async gathers */
 void b200_gemm_tc_use_filter3d(int enabled);    /* stride-1 dgrad fetches the KRSC filter through a 3-D TMA map (default on) */
 void b200_gemm_tc_use_mn32_tma(int enabled);    /* fp32 MN-major operands fetched by TMA (default on) */
+void b200_gemm_tc_cluster_reduce(int enabled);  /* split-K: splits of a tile form a cluster, reduce via DSMEM (for the calls that follow) */
 void b200_gemm_tc_split_cap(int cap);            /* upper bound on split-K for the calls that follow (default 32) */
 void b200_gemm_tc_use_im2col_tma(int enabled);  /* im2col-mode TMA for convolution activations (default on) */
 void b200_gemm_tc_use_2cta(int mode);     /* cta_group::2 cluster kernels: 0 off, 1 one tile per cluster, 2 persistent (default) */
