@@ -1319,6 +1319,12 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     attr.val.clusterDim.z = grid.z;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
+    static bool big_clusters = false;   // per template instantiation
+    if (grid.z > 8 && !big_clusters) {
+      cudaError_t e2 = cudaFuncSetAttribute(gemm_kernel<AK, BK_, BN, BF16>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      if (e2 != cudaSuccess) return static_cast<int>(e2);
+      big_clusters = true;
+    }
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_kernel<AK, BK_, BN, BF16>, a, map_a, map_b);
     if (e != cudaSuccess) return static_cast<int>(e);
     return static_cast<int>(cudaPeekAtLastError());
@@ -1427,11 +1433,11 @@ static int dispatch_bn(Args a, size_t workspace_bytes, int max_counters, int for
     splits = max(splits, 1);
   }
   const bool want_cluster = g_cluster_reduce && splits > 1 && bn <= 128 && a.peer.world <= 1;
-  if (want_cluster) splits = min(splits, 8);                // portable cluster size limit
+  if (want_cluster) splits = min(splits, g_split_cap >= 16 ? 16 : 8);   // 8 = portable cluster size, 16 = hardware maximum
   const int kps = ceil_div(k_blocks, splits) * KELEMS;
   a.splits = ceil_div(a.Kd, kps);
   a.k_per_split = kps;
-  a.cluster_reduce = want_cluster && a.splits > 1 && a.splits <= 8;
+  a.cluster_reduce = want_cluster && a.splits > 1 && a.splits <= 16;
   dim3 grid(tm, tn, a.batch > 1 ? a.batch : a.splits);
   if (bn == 32) return launch<AK, BK_, 32, BF16>(a, grid, st);
   if (bn == 64) return launch<AK, BK_, 64, BF16>(a, grid, st);

@@ -150,7 +150,7 @@ def conv_choices() -> Dict[tuple, int]:
 # split-K variants the tuner tries for a tcgen05 convolution: (upper bound on the split factor, reduce the splits
 # through a thread-block cluster's distributed shared memory instead of an L2 workspace); a choice is stored as
 # cap + 100 * cluster
-_TC_VARIANTS = ((32, 0), (1, 0), (4, 0), (12, 0), (8, 1), (4, 1), (2, 1))
+_TC_VARIANTS = ((32, 0), (1, 0), (4, 0), (12, 0), (16, 1), (8, 1), (4, 1), (2, 1))
 if os.environ.get("B200DDP_TC_VARIANTS"):          # e.g. "32,1,4,108": restrict what the tuner may pick (A/B runs)
     _TC_VARIANTS = tuple((int(v) % 100, int(v) // 100) for v in os.environ["B200DDP_TC_VARIANTS"].split(","))
 _FORCE_CLUSTER = os.environ.get("B200DDP_CLUSTER_REDUCE", "") == "1"     # testing: cluster reduction wherever K is split
