@@ -170,19 +170,48 @@ class DeviceLoader:
                 x = normalize_u8(self._images[idx]).permute(0, 3, 1, 2)   # NHWC storage, NCHW view
                 yield x, self._labels[idx]
             return
-        depth = self.slots - 1
-        sizes = {}
-        for i in range(min(depth, nb)):
-            sizes[i] = self._stage(i % self.slots, order[i * bs:(i + 1) * bs])
-        for i in range(nb):
-            slot = i % self.slots
-            b = sizes.pop(i)
-            cur = torch.cuda.current_stream(self.device)
-            cur.wait_event(self._ready[slot])
-            x = preprocess_u8(self._dev_x[slot][:b])          # fused ToTensor+Normalize, NHWC fp32
-            y = self._dev_y[slot][:b].clone()
-            self._consumed[slot].record(cur)
-            nxt = i + depth
-            if nxt < nb:
-                sizes[nxt] = self._stage(nxt % self.slots, order[nxt * bs:(nxt + 1) * bs])
-            yield x, y
+        # Host-side staging (gather into pinned memory + H2D enqueue on the copy stream) runs in a worker thread
+        # that stays up to ``slots - 1`` batches ahead, so the consumer's critical path between two training steps
+        # is only: wait-event, the normalise kernel, the label clone.  A slot is re-staged only after the consumer
+        # recorded its ``consumed`` event and released the slot.
+        import queue
+        import threading
+
+        free = [threading.Semaphore(1) for _ in range(self.slots)]
+        ready_q: "queue.Queue" = queue.Queue()
+        stop = threading.Event()
+
+        def worker() -> None:
+            try:
+                torch.cuda.set_device(self.device)
+                for i in range(nb):
+                    slot = i % self.slots
+                    free[slot].acquire()
+                    if stop.is_set():
+                        return
+                    if i >= self.slots:
+                        self._consumed[slot].synchronize()     # the GPU is done reading this slot's previous batch
+                    ready_q.put((i, self._stage(slot, order[i * bs:(i + 1) * bs])))
+            except BaseException as exc:                        # surface staging errors in the consumer
+                ready_q.put(exc)
+
+        th = threading.Thread(target=worker, name="b200ddp-stage", daemon=True)
+        th.start()
+        try:
+            for i in range(nb):
+                item = ready_q.get()
+                if isinstance(item, BaseException):
+                    raise item
+                _, b = item
+                slot = i % self.slots
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(self._ready[slot])
+                x = preprocess_u8(self._dev_x[slot][:b])          # fused ToTensor+Normalize, NHWC fp32
+                y = self._dev_y[slot][:b].clone()
+                self._consumed[slot].record(cur)
+                free[slot].release()
+                yield x, y
+        finally:
+            stop.set()
+            for sem in free:
+                sem.release()

@@ -92,7 +92,8 @@ class TrainStep:
             with torch.cuda.stream(cap_stream):
                 self._ddp.reducer.attach_hooks()
         try:
-            with torch.cuda.graph(graph, stream=cap_stream):
+            # thread_local: the data loader's staging thread keeps issuing copies while the step is captured
+            with torch.cuda.graph(graph, stream=cap_stream, capture_error_mode="thread_local"):
                 loss = self._forward_loss(static_x, static_y)
                 loss.backward()
                 self.optimizer.step()

@@ -199,7 +199,7 @@ def _time_variant(fn, acts=(), iters: int = 6) -> float:
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     g = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(g, stream=side):
+    with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
         for _ in range(iters):
             buf.zero_()
             for t in acts:
