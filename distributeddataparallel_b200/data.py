@@ -177,13 +177,14 @@ class DeviceLoader:
         import queue
         import threading
 
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
         free = [threading.Semaphore(1) for _ in range(self.slots)]
         ready_q: "queue.Queue" = queue.Queue()
         stop = threading.Event()
 
         def worker() -> None:
             try:
-                torch.cuda.set_device(self.device)
+                torch.cuda.set_device(dev_index)
                 for i in range(nb):
                     slot = i % self.slots
                     free[slot].acquire()
