@@ -60,12 +60,12 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(
     float* __restrict__ save_invstd, float* zero_after, int zero_count, int M, int C, float momentum, float eps,
     int relu, int training) {
   const float inv_m = 1.f / (float)M;
-  const size_t total4 = (size_t)M * C / 4;
   const int c4n = C >> 2;
   // the LAST block only does the per-channel bookkeeping (saved statistics, running statistics, clearing the other
   // accumulator), concurrently with the blocks that normalise: its dependent L2 round trips no longer extend the kernel
   const unsigned work_blocks = gridDim.x - 1;
   if (blockIdx.x == work_blocks) {
+    if (blockIdx.y != 0) return;
     if (training) {
       for (int c = threadIdx.x; c < C; c += blockDim.x) {
         const float m = sums[c] * inv_m;
@@ -83,34 +83,59 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(
     for (int i = threadIdx.x; i < zero_count; i += blockDim.x) zero_after[i] = 0.f;
     return;
   }
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (size_t)work_blocks * blockDim.x) {
-    const int c = (int)(i % c4n) * 4;
-    float mean[4], istd[4];
+  // A thread keeps ONE channel quad for the whole kernel: scale / shift are derived once and the loop over rows is
+  // pure streaming (no per-element index arithmetic or constant reloads), four rows in flight per thread.
+  const int cw = min(c4n, 256);                               // channel quads served by this block column
+  const int rows_per_iter = 256 / cw;
+  const int my_l = threadIdx.x % cw, my_r = threadIdx.x / cw;
+  const int cq = blockIdx.y * 256 + my_l;
+  if (my_r >= rows_per_iter || cq >= c4n) return;
+  const int c = cq * 4;
+  float sc[4], sh[4];
+  {
+    const float4 g = ldg4(gamma + c), b = ldg4(beta + c);
+    const float gg[4] = {g.x, g.y, g.z, g.w}, bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
+      float m, is;
       if (training) {
-        const float m = __ldg(sums + c + j) * inv_m;
+        m = __ldg(sums + c + j) * inv_m;
         const float var = fmaxf(__ldg(sums + C + c + j) * inv_m - m * m, 0.f);
-        mean[j] = m;
-        istd[j] = rsqrtf(var + eps);
+        is = rsqrtf(var + eps);
       } else {
-        mean[j] = running_mean[c + j];
-        istd[j] = rsqrtf(running_var[c + j] + eps);
+        m = running_mean[c + j];
+        is = rsqrtf(running_var[c + j] + eps);
       }
+      sc[j] = is * gg[j];
+      sh[j] = bb[j] - m * sc[j];
     }
-    const float4 v = ldg4(x + i * 4);
-    const float4 g = ldg4(gamma + c), b = ldg4(beta + c);
+  }
+  const int row_stride = (int)work_blocks * rows_per_iter;
+  auto one = [&](float4 v, float4 r) {
     float4 o;
-    o.x = (v.x - mean[0]) * istd[0] * g.x + b.x;
-    o.y = (v.y - mean[1]) * istd[1] * g.y + b.y;
-    o.z = (v.z - mean[2]) * istd[2] * g.z + b.z;
-    o.w = (v.w - mean[3]) * istd[3] * g.w + b.w;
-    if (residual != nullptr) {
-      const float4 r = ldg4(residual + i * 4);
-      o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
-    }
+    o.x = v.x * sc[0] + sh[0] + r.x;
+    o.y = v.y * sc[1] + sh[1] + r.y;
+    o.z = v.z * sc[2] + sh[2] + r.z;
+    o.w = v.w * sc[3] + sh[3] + r.w;
     if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-    st4(out + i * 4, o);
+    return o;
+  };
+  int r = blockIdx.x * rows_per_iter + my_r;
+  for (; r + 3 * row_stride < M; r += 4 * row_stride) {
+    float4 v[4], q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t off = (size_t)(r + u * row_stride) * C + c;
+      v[u] = ldg4(x + off);
+      q[u] = residual != nullptr ? ldg4(residual + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) st4(out + (size_t)(r + u * row_stride) * C + c, one(v[u], q[u]));
+  }
+  for (; r < M; r += row_stride) {
+    const size_t off = (size_t)r * C + c;
+    const float4 q = residual != nullptr ? ldg4(residual + off) : make_float4(0.f, 0.f, 0.f, 0.f);
+    st4(out + off, one(ldg4(x + off), q));
   }
 }
 
@@ -325,8 +350,11 @@ B200_API int b200_bn_fwd_apply(const float* x, const float* sums, const float* g
                                float* zero_after, int zero_count, int M, int C, float momentum, float eps,
                                int relu, int training, cudaStream_t stream) {
   if (C % 4 != 0) return static_cast<int>(cudaErrorInvalidValue);
-  const int grid = grid_for((size_t)M * C / 4, 256 * 2, 4 * kNumSMs) + 1;      // + the bookkeeping block
-  bn_fwd_apply_kernel<<<grid, 256, 0, stream>>>(x, sums, gamma, beta, residual, out, running_mean, running_var,
+  const int chunks = ceil_div(C / 4, 256);                  // block columns of 256 channel quads
+  const int rows_per_block = max(1, 256 / min(C / 4, 256));
+  // ~2 rows per thread on small tensors (latency), up to 4 blocks per SM on large ones (bandwidth)
+  const int gx = grid_for((size_t)M, rows_per_block * 2, max(1, 4 * kNumSMs / chunks)) + 1;   // + the bookkeeping block
+  bn_fwd_apply_kernel<<<dim3(gx, chunks), 256, 0, stream>>>(x, sums, gamma, beta, residual, out, running_mean, running_var,
                                                 num_batches_tracked, save_mean, save_invstd, zero_after, zero_count,
                                                 M, C, momentum, eps, relu, training);
   B200_LAUNCH_CHECK();
