@@ -157,18 +157,33 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(
     const int c = (cbase4 + my_l) * 4;
     const float4 mu = ldg4(save_mean + c), is = ldg4(save_invstd + c);
     float4 s = make_float4(0, 0, 0, 0), q = make_float4(0, 0, 0, 0);
-    for (int r = blockIdx.x * rows_per_iter + my_r; r < M; r += gridDim.x * rows_per_iter) {
-      const size_t off = (size_t)r * C + c;
-      float4 g = ldg4(dy + off);
+    auto add_row = [&](float4 g, float4 o, float4 v) {
       if (relu) {
-        const float4 o = ldg4(out + off);
         g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
         g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
       }
-      const float4 v = ldg4(x + off);
       s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
       q.x += g.x * (v.x - mu.x) * is.x; q.y += g.y * (v.y - mu.y) * is.y;
       q.z += g.z * (v.z - mu.z) * is.z; q.w += g.w * (v.w - mu.w) * is.w;
+    };
+    const int row_stride = gridDim.x * rows_per_iter;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    int r = blockIdx.x * rows_per_iter + my_r;
+    for (; r + 2 * row_stride < M; r += 3 * row_stride) {        // three rows (up to nine 16-byte loads) in flight
+      float4 g[3], o[3], v[3];
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const size_t off = (size_t)(r + u * row_stride) * C + c;
+        g[u] = ldg4(dy + off);
+        o[u] = relu ? ldg4(out + off) : zero4;
+        v[u] = ldg4(x + off);
+      }
+#pragma unroll
+      for (int u = 0; u < 3; ++u) add_row(g[u], o[u], v[u]);
+    }
+    for (; r < M; r += row_stride) {
+      const size_t off = (size_t)r * C + c;
+      add_row(ldg4(dy + off), relu ? ldg4(out + off) : zero4, ldg4(x + off));
     }
     atomicAdd(&sh[my_l * 4 + 0], s.x); atomicAdd(&sh[my_l * 4 + 1], s.y);
     atomicAdd(&sh[my_l * 4 + 2], s.z); atomicAdd(&sh[my_l * 4 + 3], s.w);
