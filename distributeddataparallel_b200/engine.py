@@ -108,8 +108,8 @@ class TrainStep:
 
     def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         self.steps += 1
-        if not self.use_graph or not self.model.training:
-            return self._eager(data, target)
+        if not self.use_graph or not self.model.training or (self._ddp is not None and self._ddp._join_enabled):
+            return self._eager(data, target)         # join(): every iteration carries a control collective
         key = (tuple(data.shape), data.dtype, tuple(target.shape))
         entry = self._graphs.get(key)
         if entry is None:

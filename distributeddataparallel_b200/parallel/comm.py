@@ -55,6 +55,10 @@ class CommBase:
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
         self.launches = 0
+        # what the summed gradients are divided by: the world size, except inside
+        # ``DistributedDataParallel.join(divide_by_initial_world_size=False)`` where it is the number of ranks
+        # that still have data this iteration
+        self.divisor = self.world_size
 
     # bucket memory -------------------------------------------------------------------
     def allocate(self, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
@@ -85,7 +89,7 @@ class C10dComm(CommBase):
         self.launches += 1
         if self.world_size == 1:
             return _Done()
-        flat.div_(self.world_size)
+        flat.div_(self.divisor)
         work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         return _WorkHandle(work)
 

@@ -99,6 +99,7 @@ class DistributedDataParallel(nn.Module):
         self._join_enabled = False
         self._join_iterations = 0
         self._buffer_src = 0               # rank whose buffers are broadcast before each forward
+        self._join_divide_by_world = True
         self._rebuilt_bucket_sizes: List[int] = []
         self._graph_mode = False
 
@@ -270,13 +271,25 @@ class DistributedDataParallel(nn.Module):
         return torch.tensor(values, dtype=torch.int64, device=dev)
 
     def _join_poll(self, active: int) -> int:
-        """One tiny all-reduce per iteration while ``join()`` is active.  Returns the highest rank that still
-        has data (-1: none) -- that rank is the source of this iteration's buffer broadcast, as in stock DDP."""
-        t = self._control_tensor([self.rank if active else -1])
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.process_group)
+        """One tiny all-reduce per iteration while ``join()`` is active: a one-hot vector of the ranks that still
+        have data.  Returns the highest such rank (-1: none) -- that rank is the source of this iteration's
+        buffer broadcast, as in stock DDP -- and sets the gradient divisor for the iteration."""
+        t = self._control_tensor([1 if (active and r == self.rank) else 0 for r in range(self.world_size)])
+        dist.all_reduce(t, group=self.process_group)
         self._collectives["allreduce_control"] += 1
-        self._buffer_src = max(int(t.item()), 0)
-        return int(t.item())
+        flags = t.tolist()
+        n_active = int(sum(flags))
+        top = max((r for r, f in enumerate(flags) if f), default=-1)
+        self._buffer_src = max(top, 0)
+        if not self._join_divide_by_world and n_active > 0:
+            self._set_divisor(n_active)
+        return top
+
+    def _set_divisor(self, value: int) -> None:
+        comm = self._comm
+        while comm is not None:                      # a comm hook wraps the data plane it was registered over
+            comm.divisor = value
+            comm = getattr(comm, "inner", None)
 
     def _shadow_iteration(self) -> None:
         """What a rank without data does while others train: the same collectives, zero gradients."""
@@ -292,27 +305,30 @@ class DistributedDataParallel(nn.Module):
              throw_on_early_termination: bool = False):
         """Train with a different number of batches per rank (``DistributedDataParallel.join``,
         distributed.py:1798).  A rank that leaves the context first keeps matching the other ranks'
-        collectives with zero gradients (still divided by the full world size); when the last rank
-        leaves, its parameters and buffers are broadcast so every replica ends identical."""
+        collectives with zero gradients; gradients are divided by the full world size, or -- with
+        ``divide_by_initial_world_size=False`` -- by the number of ranks that still have data (the factor is
+        an argument of the reduction kernels, set per iteration).  When the last rank leaves, its parameters
+        and buffers are broadcast so every replica ends identical.  Steps run eagerly while the context is
+        active (a captured CUDA graph cannot carry the per-iteration control collective)."""
         if not enable or self.world_size == 1:
             yield
             return
-        if not divide_by_initial_world_size:
-            raise NotImplementedError("join(divide_by_initial_world_size=False): the 1/world_size factor is fused "
-                                      "into the reduction kernels; only the default is supported")
         if throw_on_early_termination:
             raise NotImplementedError("join(throw_on_early_termination=True) is not supported")
         self._join_enabled = True
         self._join_iterations = 0
+        self._join_divide_by_world = bool(divide_by_initial_world_size)
         try:
             yield
         except BaseException:
             self._join_enabled = False
+            self._set_divisor(self.world_size)
             raise
         while self._join_poll(0) >= 0:
             self._shadow_iteration()
         self._join_enabled = False
         self._buffer_src = 0
+        self._set_divisor(self.world_size)
         # the replica that trained longest (highest rank among ties) is authoritative
         key = self._control_tensor([self._join_iterations * self.world_size + self.rank])
         dist.all_reduce(key, op=dist.ReduceOp.MAX, group=self.process_group)

@@ -246,7 +246,7 @@ class P2PComm(CommBase):
 
     def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype) -> None:
         native._call("b200_allreduce", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
-                     ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.world_size),
+                     ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
                      ctypes.c_int(self._pick_algo(nbytes)), ctypes.c_int(self.max_blocks),
                      ctypes.c_void_p(stream.cuda_stream))
 
@@ -266,7 +266,7 @@ class P2PComm(CommBase):
         if self.debug_check and not capturing:
             expect = flat.detach().float().clone()
             dist.all_reduce(expect, group=self.group)
-            expect /= self.world_size
+            expect /= self.divisor
         ready = torch.cuda.Event()
         ready.record(cur)
         self.stream.wait_event(ready)

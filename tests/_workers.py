@@ -172,7 +172,7 @@ def failing_worker(rank, ws, port):
     d.cleanup()
 
 
-def join_worker(rank, ws, port, out_dir):
+def join_worker(rank, ws, port, out_dir, divide_by_world=True):
     """Uneven inputs: rank r trains 2 + 3*r iterations inside join(); ours vs stock DDP's join()."""
     d = _init(rank, ws, port)
     from torch.nn.parallel import DistributedDataParallel as StockDDP
@@ -188,7 +188,7 @@ def join_worker(rank, ws, port, out_dir):
     g = torch.Generator().manual_seed(11 + rank)
     batches = [(torch.randn(6, 8, generator=g), torch.randn(6, 4, generator=g)) for _ in range(2 + 3 * rank)]
     for model, opt in ((mine, opt_a), (stock, opt_b)):
-        with model.join():
+        with model.join(divide_by_initial_world_size=divide_by_world):
             for x, y in batches:
                 opt.zero_grad()
                 loss = ((model(x)[:, :4] - y) ** 2).mean() + 0.0 * sum(p.sum() for p in model.module.unused.parameters())
@@ -202,6 +202,6 @@ def join_worker(rank, ws, port, out_dir):
            "err_vs_stock": float((pa - pb).norm() / pb.norm()),
            "param_err": float(max((x.detach() - y.detach()).abs().max() for x, y in zip(mine.parameters(), stock.parameters()))),
            "control": mine._get_ddp_logging_data()["collectives"]["allreduce_control"],
-           "iters": len(batches)}
+           "iters": len(batches), "divisor_after": mine.comm.divisor}
     torch.save(rec, os.path.join(out_dir, f"join{rank}.pt"))
     d.cleanup()

@@ -71,16 +71,19 @@ def test_train_and_resume(tmp_path):
     assert s1["steps"] >= 7
 
 
-def test_join_uneven_inputs_matches_stock(tmp_path):
+@pytest.mark.parametrize("divide_by_world", [True, False])
+def test_join_uneven_inputs_matches_stock(tmp_path, divide_by_world):
     """DDP.join(): rank 0 runs 2 iterations, rank 1 runs 5; nobody hangs, replicas end identical and equal
-    to what stock DDP's join() produces on the same data."""
+    to what stock DDP's join() produces on the same data -- with gradients divided by the world size or by the
+    number of ranks that still have data."""
     ws = 2
-    mp.spawn(W.join_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    mp.spawn(W.join_worker, args=(ws, _port(), str(tmp_path), divide_by_world), nprocs=ws, join=True)
     for r in range(ws):
         rec = torch.load(tmp_path / f"join{r}.pt")
         assert rec["identical_across_ranks"]
         assert rec["err_vs_stock"] < 1e-5, rec
         assert rec["control"] >= rec["iters"] + 1
+        assert rec["divisor_after"] == ws
 
 
 def test_fault_injection_fail_fast():
