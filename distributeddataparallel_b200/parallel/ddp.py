@@ -100,6 +100,7 @@ class DistributedDataParallel(nn.Module):
         self._join_iterations = 0
         self._buffer_src = 0               # rank whose buffers are broadcast before each forward
         self._join_divide_by_world = True
+        self._join_throw = False
         self._rebuilt_bucket_sizes: List[int] = []
         self._graph_mode = False
 
@@ -283,6 +284,12 @@ class DistributedDataParallel(nn.Module):
         self._buffer_src = max(top, 0)
         if not self._join_divide_by_world and n_active > 0:
             self._set_divisor(n_active)
+        if self._join_throw and 0 < n_active < self.world_size:
+            # every rank sees the same vector in the same iteration, so every rank raises here together
+            self._join_enabled = False
+            self._set_divisor(self.world_size)
+            raise RuntimeError(f"Detected at least one rank that exhausted inputs. Throwing across all ranks "
+                               f"(rank {self.rank}; {n_active} of {self.world_size} ranks still had data).")
         return top
 
     def _set_divisor(self, value: int) -> None:
@@ -308,16 +315,16 @@ class DistributedDataParallel(nn.Module):
         collectives with zero gradients; gradients are divided by the full world size, or -- with
         ``divide_by_initial_world_size=False`` -- by the number of ranks that still have data (the factor is
         an argument of the reduction kernels, set per iteration).  When the last rank leaves, its parameters
-        and buffers are broadcast so every replica ends identical.  Steps run eagerly while the context is
+        and buffers are broadcast so every replica ends identical.  With ``throw_on_early_termination=True`` all
+        ranks raise ``RuntimeError`` in the iteration in which the first rank runs out instead.  Steps run eagerly while the context is
         active (a captured CUDA graph cannot carry the per-iteration control collective)."""
         if not enable or self.world_size == 1:
             yield
             return
-        if throw_on_early_termination:
-            raise NotImplementedError("join(throw_on_early_termination=True) is not supported")
         self._join_enabled = True
         self._join_iterations = 0
         self._join_divide_by_world = bool(divide_by_initial_world_size)
+        self._join_throw = bool(throw_on_early_termination)
         try:
             yield
         except BaseException:

@@ -205,3 +205,26 @@ def join_worker(rank, ws, port, out_dir, divide_by_world=True):
            "iters": len(batches), "divisor_after": mine.comm.divisor}
     torch.save(rec, os.path.join(out_dir, f"join{rank}.pt"))
     d.cleanup()
+
+
+def join_throw_worker(rank, ws, port, out_dir):
+    """join(throw_on_early_termination=True): rank 0 runs out after 2 iterations -> every rank raises."""
+    d = _init(rank, ws, port)
+    d.ops.set_native(False)
+    torch.manual_seed(5)
+    mine = d.DDP(TinyNet(), comm="c10d")
+    opt = torch.optim.SGD(mine.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(11 + rank)
+    done, msg = 0, ""
+    try:
+        with mine.join(throw_on_early_termination=True):
+            for _ in range(2 + 3 * rank):
+                x, y = torch.randn(6, 8, generator=g), torch.randn(6, 4, generator=g)
+                opt.zero_grad()
+                (((mine(x) - y) ** 2).mean() + 0.0 * sum(p.sum() for p in mine.module.unused.parameters())).backward()
+                opt.step()
+                done += 1
+    except RuntimeError as exc:
+        msg = str(exc)
+    torch.save({"done": done, "msg": msg}, os.path.join(out_dir, f"throw{rank}.pt"))
+    d.cleanup()

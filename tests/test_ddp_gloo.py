@@ -86,6 +86,14 @@ def test_join_uneven_inputs_matches_stock(tmp_path, divide_by_world):
         assert rec["divisor_after"] == ws
 
 
+def test_join_throw_on_early_termination(tmp_path):
+    ws = 2
+    mp.spawn(W.join_throw_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    recs = [torch.load(tmp_path / f"throw{r}.pt") for r in range(ws)]
+    assert all("exhausted inputs" in r["msg"] for r in recs), recs
+    assert recs[0]["done"] == 2 and recs[1]["done"] == 2        # rank 1 stops in the iteration rank 0 misses
+
+
 def test_fault_injection_fail_fast():
     ws = 2
     with pytest.raises(Exception) as ei:
