@@ -111,7 +111,8 @@ class DistributedDataParallel(nn.Module):
         if init_sync and self.world_size > 1:
             self._verify_params_across_processes()
             self._sync_module_states()
-        self._buffers_for_sync = [b for b in module.buffers()]
+        ignored = set(getattr(module, "_ddp_params_and_buffers_to_ignore", ()) or ())
+        self._buffers_for_sync = [b for n, b in module.named_buffers() if n not in ignored]
 
         # Iteration 0: every gradient in ONE bucket (size limit "infinite") unless unused
         # parameters must be searched, exactly like the stock wrapper (distributed.py:1224).
@@ -130,12 +131,30 @@ class DistributedDataParallel(nn.Module):
     # -- construction helpers --------------------------------------------------------------
     @staticmethod
     def _named_params(module: nn.Module):
+        # stock contract (distributed.py:732-736, 2331): names listed in ``module._ddp_params_and_buffers_to_ignore``
+        # are neither reduced nor broadcast
+        ignored = set(getattr(module, "_ddp_params_and_buffers_to_ignore", ()) or ())
         seen = set()
         for mod_name, mod in module.named_modules():
             for pname, p in mod.named_parameters(recurse=False):
-                if p.requires_grad and id(p) not in seen:
+                fqn = f"{mod_name}.{pname}" if mod_name else pname
+                if p.requires_grad and id(p) not in seen and fqn not in ignored:
                     seen.add(id(p))
-                    yield (f"{mod_name}.{pname}" if mod_name else pname), p
+                    yield fqn, p
+
+    @staticmethod
+    def _set_params_and_buffers_to_ignore_for_model(module: nn.Module, params_and_buffers_to_ignore) -> None:
+        """Call before wrapping: fully-qualified parameter / buffer names DDP must leave alone."""
+        module._ddp_params_and_buffers_to_ignore = list(params_and_buffers_to_ignore)
+
+    def _set_static_graph(self) -> None:
+        """Accepted for API compatibility: the whole-step CUDA graph (engine.TrainStep) is this framework's
+        static-graph mode; the eager reducer does not need the hint."""
+        self.static_graph = True
+
+    def will_sync_module_buffers(self) -> bool:
+        return (self.require_backward_grad_sync and self.broadcast_buffers and self.world_size > 1
+                and len(self._buffers_for_sync) > 0)
 
     def _make_comm(self, comm) -> CommBase:
         if isinstance(comm, CommBase):
@@ -197,8 +216,9 @@ class DistributedDataParallel(nn.Module):
                 raise RuntimeError(f"DDP expects the same model across all ranks, but rank {self.rank}: {msg}")
 
     def _sync_module_states(self, src: int = 0) -> None:
-        params = [p.detach() for p in self.module.parameters()]
-        bufs = [b.detach() for b in self.module.buffers()]
+        ignored = set(getattr(self.module, "_ddp_params_and_buffers_to_ignore", ()) or ())
+        params = [p.detach() for n, p in self.module.named_parameters() if n not in ignored]
+        bufs = [b.detach() for n, b in self.module.named_buffers() if n not in ignored]
         self._collectives["broadcast"] += broadcast_coalesced(
             self._comm, params + bufs, self.broadcast_bucket_size, src=src)
 

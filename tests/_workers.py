@@ -228,3 +228,31 @@ def join_throw_worker(rank, ws, port, out_dir):
         msg = str(exc)
     torch.save({"done": done, "msg": msg}, os.path.join(out_dir, f"throw{rank}.pt"))
     d.cleanup()
+
+
+def ignore_worker(rank, ws, port, out_dir):
+    """module._ddp_params_and_buffers_to_ignore: the listed parameter / buffer is neither broadcast nor reduced."""
+    d = _init(rank, ws, port)
+    d.ops.set_native(False)
+    torch.manual_seed(100 + rank)
+    net = TinyNet()
+    d.DDP._set_params_and_buffers_to_ignore_for_model(net, ["unused.weight", "bn.running_mean"])
+    before = net.unused.weight.detach().clone()
+    mine = d.DDP(net, comm="c10d")
+    kept_local = torch.equal(net.unused.weight.detach(), before)
+    x = torch.randn(6, 8, generator=torch.Generator().manual_seed(rank))
+    mine(x, use_unused=True).sum().backward()
+    gl = [torch.zeros_like(net.unused.weight.grad) for _ in range(ws)]
+    dist.all_gather(gl, net.unused.weight.grad)
+    al = [torch.zeros_like(net.a.weight.grad) for _ in range(ws)]
+    dist.all_gather(al, net.a.weight.grad)
+    rm = [torch.zeros_like(net.bn.running_mean) for _ in range(ws)]
+    dist.all_gather(rm, net.bn.running_mean)
+    mine(x, use_unused=True)                      # a second forward would have re-broadcast rank 0's buffers
+    rv = [torch.zeros_like(net.bn.running_var) for _ in range(ws)]
+    dist.all_gather(rv, net.bn.running_var)
+    torch.save({"kept_local": kept_local, "ignored_grad_differs": not torch.equal(gl[0], gl[1]),
+                "other_grad_equal": torch.equal(al[0], al[1]), "ignored_buffer_differs": not torch.equal(rm[0], rm[1]),
+                "names": mine._param_names, "will_sync": mine.will_sync_module_buffers()},
+               os.path.join(out_dir, f"ign{rank}.pt"))
+    d.cleanup()

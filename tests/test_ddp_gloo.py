@@ -94,6 +94,16 @@ def test_join_throw_on_early_termination(tmp_path):
     assert recs[0]["done"] == 2 and recs[1]["done"] == 2        # rank 1 stops in the iteration rank 0 misses
 
 
+def test_params_and_buffers_to_ignore(tmp_path):
+    ws = 2
+    mp.spawn(W.ignore_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    for r in range(ws):
+        rec = torch.load(tmp_path / f"ign{r}.pt")
+        assert rec["kept_local"] and rec["ignored_grad_differs"] and rec["other_grad_equal"], rec
+        assert rec["ignored_buffer_differs"] and rec["will_sync"]
+        assert "unused.weight" not in rec["names"] and "unused.bias" in rec["names"]
+
+
 def test_fault_injection_fail_fast():
     ws = 2
     with pytest.raises(Exception) as ei:
