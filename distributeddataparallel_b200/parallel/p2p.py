@@ -183,6 +183,7 @@ class P2PComm(CommBase):
         self.device = device
         self.algo = algo
         self.max_blocks = int(max_blocks or os.environ.get("B200DDP_COMM_BLOCKS", 32))
+        self.last_blocks = int(os.environ.get("B200DDP_COMM_BLOCKS_LAST", self.max_blocks))
         self.oneshot_max = int(os.environ.get("B200DDP_ONESHOT_MAX_BYTES", 256 << 10))
         self._arena_bytes = arena_bytes
         self.arena: Optional[SymmetricArena] = None
@@ -244,10 +245,11 @@ class P2PComm(CommBase):
             return 3
         return 2
 
-    def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype) -> None:
+    def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype,
+                      blocks: Optional[int] = None) -> None:
         native._call("b200_allreduce", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
                      ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
-                     ctypes.c_int(self._pick_algo(nbytes)), ctypes.c_int(self.max_blocks),
+                     ctypes.c_int(self._pick_algo(nbytes)), ctypes.c_int(blocks or self.max_blocks),
                      ctypes.c_void_p(stream.cuda_stream))
 
     def launch(self, index: int, flat: torch.Tensor, is_last: bool):
@@ -274,7 +276,10 @@ class P2PComm(CommBase):
         if self.timing and not capturing:
             t0 = torch.cuda.Event(enable_timing=True)
             t0.record(self.stream)
-        self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype)
+        # the last bucket of a backward pass has nothing left to overlap with: it may use more of the chip
+        # (every rank takes the same decision, so the block counts agree)
+        self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype,
+                           blocks=self.last_blocks if is_last else None)
         done = torch.cuda.Event(enable_timing=t0 is not None)
         done.record(self.stream)
         if t0 is not None:
