@@ -53,6 +53,7 @@ class TrainConfig:
     seq_len: int = 1024                # GPT-2 only
     image_size: int = 32               # 32 for CIFAR shaped, 224 for ImageNet shaped
     print_throughput: bool = False
+    print_ddp_stats: bool = False      # rank 0 prints the reducer / data-plane summary when training ends
     extra: dict = field(default_factory=dict)
 
     def resolved_device(self) -> str:
@@ -126,6 +127,9 @@ def build_parser() -> argparse.ArgumentParser:
     _add_bool(p, "native-ops", d.native_ops, "run the model on the sm_100a kernels")
     _add_bool(p, "broadcast-buffers", d.broadcast_buffers, "re-broadcast BN buffers from rank 0 each forward")
     _add_bool(p, "print-throughput", d.print_throughput, "print samples/s next to the loss line")
+    _add_bool(p, "print-ddp-stats", d.print_ddp_stats,
+              "rank 0 prints bucket sizes, collective counts and (with B200DDP_COMM_TIMING=1) per-bucket "
+              "all-reduce time / bus GB/s when training ends")
     return p
 
 

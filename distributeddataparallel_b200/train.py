@@ -54,6 +54,31 @@ def build_optimizer(cfg: TrainConfig, params):
     return SGD(params, lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay)   # dpp.py:41
 
 
+def format_ddp_stats(log: dict, samples: int, seconds: float) -> str:
+    """Human-readable summary of ``DistributedDataParallel._get_ddp_logging_data()``: bucket layout,
+    collectives issued, host-timed forward / backward / communication shares and -- when the P2P data plane ran with
+    ``B200DDP_COMM_TIMING=1`` -- device-timed bucket all-reduce time and bus bandwidth."""
+    lines = [f"[ddp] {samples} samples in {seconds:.2f} s = {samples / max(seconds, 1e-9):.0f} samples/s (wall clock)",
+             f"[ddp] world {log.get('world_size')} backend {log.get('backend_name')} data plane {log.get('comm_backend')} "
+             f"hook {log.get('comm_hook')}",
+             f"[ddp] parameters {log.get('num_parameter_tensors')} tensors / {log.get('total_parameter_size_bytes')} B; "
+             f"buckets first iteration {log.get('initial_bucket_sizes')} -> rebuilt {log.get('rebuilt_bucket_sizes')}",
+             f"[ddp] iterations {log.get('iteration')}, buckets reduced {log.get('num_buckets_reduced')}, "
+             f"collectives {log.get('collectives')}"]
+    if log.get("avg_backward_compute_time_ms") is not None:
+        bwd = float(log.get("avg_backward_compute_time_ms") or 0.0)
+        comm = float(log.get("avg_backward_comm_time_ms") or 0.0)
+        overlap = float(log.get("avg_backward_compute_comm_overlap_time_ms") or 0.0)
+        exposed = max(comm - overlap, 0.0)
+        lines.append(f"[ddp] host-timed per iteration: forward {float(log.get('avg_forward_compute_time_ms') or 0):.3f} ms, "
+                     f"backward {bwd:.3f} ms, communication {comm:.3f} ms of which {exposed:.3f} ms not overlapped")
+    cs = log.get("comm_stats") or {}
+    if "avg_bucket_allreduce_us" in cs:
+        lines.append(f"[ddp] device-timed bucket all-reduce: {cs['avg_bucket_allreduce_us']:.1f} us average over "
+                     f"{cs['timed_buckets']} buckets, bus bandwidth {cs['bus_bandwidth_GBs']:.0f} GB/s")
+    return "\n".join(lines)
+
+
 def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig] = None) -> dict:
     cfg = cfg or TrainConfig()
     device_type = cfg.resolved_device()
@@ -115,6 +140,8 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
             break
     stats = {"steps": global_step, "loss_history": history, "graph_replays": step_fn.replays,
              "ddp": model._get_ddp_logging_data()}
+    if cfg.print_ddp_stats and rank == 0:
+        print(format_ddp_stats(stats["ddp"], seen * world_size, time.time() - t0), flush=True)
     del step_fn
     cleanup()                                                               # dpp.py:57
     return stats

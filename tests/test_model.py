@@ -64,3 +64,18 @@ def test_resnet50_keys():
     b = tv.models.resnet50(weights=None).state_dict()
     assert list(a.keys()) == list(b.keys())
     assert all(a[k].shape == b[k].shape for k in a)
+
+
+def test_ddp_stats_summary_formatting():
+    from distributeddataparallel_b200.train import format_ddp_stats
+
+    log = {"world_size": 8, "backend_name": "nccl", "comm_backend": "p2p", "comm_hook": "builtin",
+           "num_parameter_tensors": 62, "total_parameter_size_bytes": 44726568, "initial_bucket_sizes": [44726568],
+           "rebuilt_bucket_sizes": [9461800, 26494976, 8769792], "iteration": 10, "num_buckets_reduced": 28,
+           "collectives": {"broadcast": 3}, "avg_forward_compute_time_ms": 0.4, "avg_backward_compute_time_ms": 0.6,
+           "avg_backward_comm_time_ms": 0.5, "avg_backward_compute_comm_overlap_time_ms": 0.45,
+           "comm_stats": {"avg_bucket_allreduce_us": 57.0, "timed_buckets": 27, "bus_bandwidth_GBs": 455.0}}
+    text = format_ddp_stats(log, 2560, 0.01)
+    assert "256000 samples/s" in text and "data plane p2p" in text
+    assert "rebuilt [9461800, 26494976, 8769792]" in text and "iterations 10" in text
+    assert "0.050 ms not overlapped" in text and "bus bandwidth 455 GB/s" in text
