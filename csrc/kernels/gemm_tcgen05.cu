@@ -123,6 +123,9 @@ struct Args {
                                // 4 im2col fp32 MN-major (wgrad), 5 filter as {C, RS, K} boxes with flipped taps (dgrad)
   const void* filter3d;        // != nullptr: WEIGHT_T_MN operand is the original KRSC filter, fetched by mode 5
   int filter_k;                // its K (number of filters); its C is the tile's mn extent
+  // window offset (r, s) of the running convolution -> tap of the ORIGINAL filter:
+  //   ((f_r0 + f_rstep * r) * f_S + (f_s0 + f_sstep * s)); filter_rs = R*S of the original filter
+  int f_r0, f_rstep, f_s0, f_sstep, f_S, filter_rs;
   PeerReduce peer;             // world > 1: fused all-reduce epilogue (needs splits == 1, row-major out)
   // causal attention structure (batched calls): 1 = output tile is entirely above the diagonal -> skip it
   // (S = QK^T, dP = dO V^T); 2 = reduction index is the key, only keys <= query row matter (P V, dS K);
@@ -420,7 +423,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
             a.g.fS.divmod(rs, r, sx);
             // dgrad as a forward convolution of dY: the filter tap that meets window offset (r, s) is the mirrored one,
             // and the reduction "channel" c0 is the filter index k'
-            const int rs_flip = a.g.R * a.g.S - 1 - rs;
+            const int rs_flip = (a.f_r0 + a.f_rstep * r) * a.f_S + (a.f_s0 + a.f_sstep * sx);
             if (a.tma_a == 5)
               for (int bx = 0; bx < BM / 32; ++bx) tma_load_3d(smem_a + s * A_STAGE + bx * 4096, &map_a, m0 + bx * 32, rs_flip, c0, &full_bar[s]);
             if (a.tma_b == 5)
@@ -1248,6 +1251,25 @@ __global__ void __launch_bounds__(256) flip_transpose_filter_kernel(const float*
   }
 }
 
+// Stride-2 dgrad by output parity: class (a, b) = input pixels (2i + a, 2j + b) is a stride-1 convolution of dY
+// with the taps r = a + pad (mod 2), s = b + pad (mod 2) only.  Each class is computed into a compact
+// [Nb, H2, W2, C] buffer by the forward kernels and interleaved into dX here (float4 per thread).
+// tmp == nullptr: the class has no tap at all (e.g. three of the four classes of a 1x1 stride-2 filter) -> zeros.
+__global__ void __launch_bounds__(256) scatter_parity_kernel(const float* __restrict__ tmp, float* __restrict__ dx, int Nb, int H,
+                                                             int W, int C, int H2, int W2, int pa, int pb) {
+  const int c4n = C >> 2;
+  const size_t total = (size_t)Nb * H2 * W2 * c4n;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c4 = (int)(i % c4n);
+    size_t pix = i / c4n;
+    const int j = (int)(pix % W2);
+    pix /= W2;
+    const int ii = (int)(pix % H2), n = (int)(pix / H2);
+    const float4 v = tmp != nullptr ? reinterpret_cast<const float4*>(tmp)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4*>(dx + (((size_t)n * H + 2 * ii + pa) * W + 2 * j + pb) * C)[c4] = v;
+  }
+}
+
 // ---- host side ------------------------------------------------------------------------------------
 // 2-D row-major global matrix [outer x inner] with `pitch` elements per row; box [box_outer x box_inner];
 // 128-byte swizzle; out-of-range parts of a box are zero-filled.
@@ -1260,6 +1282,7 @@ static bool g_use_tma = true;
 static bool g_cluster_reduce = false;  // split-K partials reduced through distributed shared memory (tuner-selected)
 static int g_split_cap = 32;          // upper bound on the split-K factor (per-shape tuning knob, see ops/native.py)
 static bool g_use_im2col_tma = true;
+static bool g_use_s2_dgrad = true;    // stride-2 dgrad of large images by output parity (four stride-1 problems + interleave)
 static bool g_use_filter3d = true;    // stride-1 dgrad reads the KRSC filter through a 3-D TMA descriptor (no re-layout kernel)
 static bool g_use_mn32_tma = true;    // fp32 MN-major operands by TMA (SWIZZLE_128B_ATOM_32B)
 static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom& g, int channels, int pixels) {
@@ -1284,7 +1307,7 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     else if (BK_ == DENSE_MN && !BF16 && g_use_mn32_tma &&
              tma_make_map_2d(&map_b, a.b, false, a.N, a.Kd, a.ldb, 32, KELEMS, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B)) a.tma_b = 3;
     if (!BF16 && a.filter3d != nullptr) {                   // required: the gather code cannot serve this operand
-      const int rs = a.g.R * a.g.S;
+      const int rs = a.filter_rs;
       if (AK == WEIGHT_T_MN) { if (!tma_make_map_filter_3d(&map_a, a.filter3d, a.filter_k, rs, a.M)) return 801; a.tma_a = 5; }
       if (BK_ == WEIGHT_T_MN) { if (!tma_make_map_filter_3d(&map_b, a.filter3d, a.filter_k, rs, a.N)) return 801; a.tma_b = 5; }
     }
@@ -1456,6 +1479,7 @@ static bool ptr16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u)
 // Switch the TMA operand path on/off (default on); off = every operand is gathered with cp.async.
 B200_API void b200_gemm_tc_use_tma(int enabled) { b200::tc::g_use_tma = enabled != 0; }
 // 2-CTA (cta_group::2, 256-row cluster tile) kernels for large dense GEMMs.
+B200_API void b200_gemm_tc_use_s2_dgrad(int enabled) { b200::tc::g_use_s2_dgrad = enabled != 0; }
 B200_API void b200_gemm_tc_use_filter3d(int enabled) { b200::tc::g_use_filter3d = enabled != 0; }
 B200_API void b200_gemm_tc_use_mn32_tma(int enabled) { b200::tc::g_use_mn32_tma = enabled != 0; }
 B200_API void b200_gemm_tc_split_cap(int cap) { b200::tc::g_split_cap = cap < 1 ? 1 : cap; }
@@ -1587,6 +1611,7 @@ B200_API int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, in
     f.g = make_geom(Nb, a.g.P, a.g.Q, K, C, R, S, 1, R - 1 - pad);
     f.Kd = R * S * K; f.workspace = workspace; f.counters = counters; f.error = error; f.out = dx; f.ldo = C;
     f.filter3d = w; f.filter_k = K;
+    f.f_r0 = R - 1; f.f_rstep = -1; f.f_s0 = S - 1; f.f_sstep = -1; f.f_S = S; f.filter_rs = R * S;   // mirrored taps
     int rc;
     if (pixels >= 1024 || C < 128) {
       f.a = dy; f.b = w; f.lda = K; f.ldb = C; f.M = pixels; f.N = C;
@@ -1596,6 +1621,75 @@ B200_API int b200_conv2d_dgrad_tc(const float* dy, const float* w, float* dx, in
       rc = dispatch_bn<WEIGHT_T_MN, IM2COL_K, false>(f, workspace_bytes, max_counters, 0, stream);
     }
     if (rc != 801) return rc;
+  }
+  // Stride-2 filters on large images: the gather kernel multiplies three zero taps out of four.  Input pixels of one parity
+  // class (h % 2, w % 2) only meet the filter taps r = a + pad, s = b + pad (mod 2), and for those dX is a stride-1
+  // convolution of dY -- so each class goes through the TMA-fed forward kernels into a compact buffer at the head of
+  // the workspace and is interleaved into dX afterwards.
+  if (g_use_s2_dgrad && g_use_im2col_tma && g_use_mn32_tma && g_use_tma && g_use_filter3d && stride == 2 && R == S &&
+      K % 32 == 0 && C % 4 == 0 && pixels >= 16384 && workspace != nullptr) {
+    const int P = a.g.P, Q = a.g.Q;
+    bool ok = true;
+    // per class and axis: taps r0, r0 - 2, ... (n of them) reading dY index i + t, t = t_min .. t_min + n - 1
+    struct Axis { int n, r_first, t_min, ext; } ax[2][2];            // [axis h/w][parity]
+    for (int axis = 0; axis < 2 && ok; ++axis)
+      for (int par = 0; par < 2; ++par) {
+        const int dim = axis == 0 ? H : W;
+        Axis& e = ax[axis][par];
+        e.ext = (dim - par + 1) / 2;                                 // pixels of this parity along the axis
+        e.n = 0; e.r_first = 0; e.t_min = 0;
+        int t_max = 0;
+        for (int r = 0; r < R; ++r) {
+          if (((par + pad - r) & 1) != 0) continue;
+          const int t = (par + pad - r) / 2;                         // exact: numerator is even
+          if (e.n == 0) { e.t_min = t; t_max = t; }
+          e.t_min = min(e.t_min, t);
+          t_max = max(t_max, t);
+          ++e.n;
+        }
+        if (e.n > 0) e.r_first = par + pad - 2 * e.t_min;            // tap that meets window offset 0
+        (void)t_max;
+      }
+    const size_t tmp_bytes = (size_t)Nb * ax[0][0].ext * ax[1][0].ext * C * sizeof(float);   // parity (0,0) is the largest
+    const size_t ws_left = workspace_bytes > tmp_bytes ? ((workspace_bytes - tmp_bytes) & ~(size_t)255) : 0;
+    for (int pa = 0; pa < 2 && ok; ++pa)
+      for (int pb = 0; pb < 2; ++pb)
+        if (ax[0][pa].n > 0 && ax[1][pb].n > 0 && (ax[0][pa].t_min != ax[1][pb].t_min || ax[0][pa].t_min > 0))
+          ok = false;                                                 // Geom carries one (non-negative) padding
+    if (ok && tmp_bytes > 0 && ws_left >= (1u << 20)) {
+      float* tmp = workspace;
+      float* ws2 = reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + ((tmp_bytes + 255) & ~(size_t)255));
+      bool wrote = false, give_up = false;
+      // classes that need a GEMM first, so that an unsupported configuration is detected before dX is touched
+      for (int pass = 0; pass < 2 && !give_up; ++pass)
+      for (int pa = 0; pa < 2 && !give_up; ++pa)
+        for (int pb = 0; pb < 2; ++pb) {
+          if ((pass == 0) != (ax[0][pa].n > 0 && ax[1][pb].n > 0)) continue;
+          const Axis &eh = ax[0][pa], &ew = ax[1][pb];
+          if (eh.ext == 0 || ew.ext == 0) continue;
+          const size_t cells = (size_t)Nb * eh.ext * ew.ext * (C / 4);
+          const size_t want = (cells + 255) / 256, cap = (size_t)(8 * kNumSMs);
+          const int sg = (int)(want < cap ? want : cap);
+          if (eh.n == 0 || ew.n == 0) {                               // no tap reaches this class: zeros
+            scatter_parity_kernel<<<sg, 256, 0, stream>>>(nullptr, dx, Nb, H, W, C, eh.ext, ew.ext, pa, pb);
+            continue;
+          }
+          Args f{};
+          f.g = make_geom(Nb, P, Q, K, C, eh.n, ew.n, 1, -eh.t_min);  // dY is the input; eh.n x ew.n taps, stride 1
+          f.g.P = eh.ext; f.g.Q = ew.ext;                             // output grid = this parity class
+          f.g.fP = make_fastdiv(f.g.P); f.g.fQ = make_fastdiv(f.g.Q);
+          f.Kd = eh.n * ew.n * K; f.workspace = ws2; f.counters = counters; f.error = error; f.out = tmp; f.ldo = C;
+          f.filter3d = w; f.filter_k = K;
+          f.f_r0 = eh.r_first; f.f_rstep = -2; f.f_s0 = ew.r_first; f.f_sstep = -2; f.f_S = S; f.filter_rs = R * S;
+          f.a = dy; f.b = w; f.lda = K; f.ldb = C; f.M = Nb * eh.ext * ew.ext; f.N = C;
+          const int rc = dispatch_bn<IM2COL_K, WEIGHT_T_MN, false>(f, ws_left, max_counters, 0, stream);
+          if (rc == 801 && !wrote) { give_up = true; break; }         // descriptors unavailable: nothing written yet
+          if (rc != 0) return rc;
+          scatter_parity_kernel<<<sg, 256, 0, stream>>>(tmp, dx, Nb, H, W, C, eh.ext, ew.ext, pa, pb);
+          wrote = true;
+        }
+      if (!give_up) return static_cast<int>(cudaPeekAtLastError());
+    }
   }
   const size_t wt_bytes = (size_t)C * R * S * K * sizeof(float);
   if (!pointwise && g_use_im2col_tma && g_use_tma && stride == 1 && R == S && R - 1 - pad >= 0 && K % 32 == 0 && workspace &&

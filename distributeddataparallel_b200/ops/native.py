@@ -40,6 +40,8 @@ def load_library():
         getattr(lib, name).restype = ctypes.c_int
     if "B200DDP_2CTA" in os.environ:       # 0 off, 1 one tile per cluster, 2 persistent (library default)
         lib.b200_gemm_tc_use_2cta(ctypes.c_int(int(os.environ["B200DDP_2CTA"])))
+    if "B200DDP_S2_DGRAD" in os.environ:
+        lib.b200_gemm_tc_use_s2_dgrad(ctypes.c_int(int(os.environ["B200DDP_S2_DGRAD"])))
     if "B200DDP_FILTER3D" in os.environ:
         lib.b200_gemm_tc_use_filter3d(ctypes.c_int(int(os.environ["B200DDP_FILTER3D"])))
     if "B200DDP_MN32_TMA" in os.environ:

@@ -138,6 +138,7 @@ int b200_peer_reduce_bytes(void);
 int b200_gemm_tc_peer(const void* A, const void* B, const void* bias, int M, int N, int K, int mode, int flags,
                       const long long* desc, const void* peer, unsigned* error, cudaStream_t stream);
 void b200_gemm_tc_use_tma(int enabled);   /* dense operands via TMA (default) or cp.async gathers */
+void b200_gemm_tc_use_s2_dgrad(int enabled);    /* stride-2 dgrad of >= 16384-pixel inputs as four stride-1 parity problems (default on) */
 void b200_gemm_tc_use_filter3d(int enabled);    /* stride-1 dgrad fetches the KRSC filter through a 3-D TMA map (default on) */
 void b200_gemm_tc_use_mn32_tma(int enabled);    /* fp32 MN-major operands fetched by TMA (default on) */
 void b200_gemm_tc_cluster_reduce(int enabled);  /* split-K: splits of a tile form a cluster, reduce via DSMEM (for the calls that follow) */

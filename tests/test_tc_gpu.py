@@ -108,3 +108,29 @@ def test_rgb_stem_runs_on_tensor_cores_with_a_zero_fourth_channel(nat):
     y2 = nat.conv2d(xg, w, 2, 3)
     assert nat.ffma_launches == ff1 + 1
     assert _rel(y2, yd) < 1e-5
+
+
+@pytest.mark.parametrize("c,k,r,pad", [(64, 128, 3, 1), (64, 128, 1, 0)])
+def test_stride2_dgrad_by_parity_classes(nat, c, k, r, pad):
+    """Stride-2 dgrad of a large image runs as four stride-1 problems (one per input-pixel parity) through the
+    TMA-fed forward kernels and is interleaved into dX; it must agree with the gather kernel and with fp64."""
+    import ctypes
+
+    lib = nat.load_library()
+    nat.set_tensor_cores(True)
+    torch.manual_seed(0)
+    x = _cl(torch.randn(8, c, 56, 56, device="cuda")).requires_grad_(True)        # 25 088 input pixels >= 16 384
+    w = _cl(torch.randn(k, c, r, r, device="cuda") * 0.05).requires_grad_(True)
+    y = nat.conv2d(x, w, 2, pad)
+    dy = _cl(torch.randn_like(y))
+    got = {}
+    try:
+        for flag in (1, 0):
+            lib.b200_gemm_tc_use_s2_dgrad(ctypes.c_int(flag))
+            (got[flag],) = torch.autograd.grad(nat.conv2d(x, w, 2, pad), x, dy)
+    finally:
+        lib.b200_gemm_tc_use_s2_dgrad(ctypes.c_int(1))
+    ref = torch.autograd.grad(F.conv2d(x.double(), w.double(), None, 2, pad), x, dy.double())[0]
+    assert _rel(got[1], ref) < 2e-3 and _rel(got[0], ref) < 2e-3
+    assert _rel(got[1], got[0]) < 2e-3
+    assert nat.tc_error_word() == 0
