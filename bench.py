@@ -93,6 +93,67 @@ def barrier(world):
     torch.cuda.synchronize()
 
 
+def load_clock_sampler():
+    """``ClockSampler`` loaded by file path: importing the package would map this repository's native
+    libraries into the process, which the reference arm must never do."""
+    import importlib.util
+
+    path = os.path.join(ROOT, "distributeddataparallel_b200", "utils", "clocks.py")
+    spec = importlib.util.spec_from_file_location("_b200ddp_clocks", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.ClockSampler
+
+
+def find_reference(rank: int, world: int):
+    """Directory holding the unmodified ``dpp.py``: ``baseline/_ref`` (written by ``build()``), else installed
+    now from ``$B200DDP_REFERENCE`` / ``/root/reference`` (byte-identical copy), else None."""
+    import shutil
+
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    dst = os.path.join(ref_dir, "dpp.py")
+    if os.path.isfile(dst):
+        return ref_dir
+    cands = [os.environ.get("B200DDP_REFERENCE"), "/root/reference"]
+    for c in cands:
+        if not c:
+            continue
+        src = os.path.join(c, "dpp.py") if os.path.isdir(c) else c
+        if not os.path.isfile(src):
+            continue
+        try:
+            if int(os.environ.get("LOCAL_RANK", rank)) == 0:
+                os.makedirs(ref_dir, exist_ok=True)
+                tmp = dst + f".tmp{os.getpid()}"
+                shutil.copyfile(src, tmp)
+                os.replace(tmp, dst)
+            else:
+                for _ in range(200):
+                    if os.path.isfile(dst):
+                        break
+                    time.sleep(0.05)
+            if os.path.isfile(dst) and open(dst, "rb").read() == open(src, "rb").read():
+                return ref_dir
+        except OSError:
+            pass
+        return os.path.dirname(os.path.abspath(src))       # read-only tree: import it from where it is
+    return None
+
+
+def loaded_native_libs():
+    """Shared objects from this repository mapped into the current process (the reference arm must show [])."""
+    out = set()
+    try:
+        with open("/proc/self/maps") as f:
+            for line in f:
+                path = line.split()[-1] if line.strip() else ""
+                if path.startswith(ROOT) and ".so" in path and "/baseline/" not in path:
+                    out.add(os.path.relpath(path, ROOT))
+    except OSError:
+        pass
+    return sorted(out)
+
+
 _REAL_STDOUT = None
 
 
@@ -121,8 +182,8 @@ def run_ours(args, rank, local_rank, world):
     import torch.distributed as dist
 
     import distributeddataparallel_b200 as d
-    from distributeddataparallel_b200.utils.clocks import ClockSampler
 
+    ClockSampler = load_clock_sampler()
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
@@ -153,7 +214,7 @@ def run_ours(args, rank, local_rank, world):
         native = native_mod
 
     # ---- internal settle (bucket rebuild, graph capture) + W warm-up steps ------------------
-    sampler = ClockSampler(gpu_index=local_rank, period_ms=50).start()     # nvidia-smi takes a while to come up
+    sampler = ClockSampler(gpu_index=local_rank).start()
     for i in range(4 + W):
         step(xs[i % pool_n], pool_y[i % pool_n])
     sampler.wait_for_samples(1)
@@ -172,7 +233,8 @@ def run_ours(args, rank, local_rank, world):
     torch.cuda.synchronize()
     barrier(world)
     dev_ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
-    clocks = sampler.stop(clock_mark)
+    clock_end = sampler.mark()
+    clocks = sampler.summary(clock_mark, clock_end)
     launches = 0
     if native:
         eager_launches = native.launch_count() - launches_before
@@ -201,9 +263,17 @@ def run_ours(args, rank, local_rank, world):
     e2e_ms = max_over_ranks(max(c0.elapsed_time(c1), e2e_wall_ms), world, dev)
     barrier(world)
 
+    sampler.stop()
     samples = K * B * world
     value = samples / (dev_ms / 1e3)
     log = ddp._get_ddp_logging_data()
+    # ---- the other half of the metric: device-timed bucket all-reduce at this N -------------------------
+    bucket_sizes = log.get("rebuilt_bucket_sizes") or log.get("initial_bucket_sizes") or []
+    allreduce = []
+    timer = getattr(ddp.comm, "time_allreduce", None)
+    if world > 1 and timer is not None:
+        for nbytes in bucket_sizes:
+            allreduce.append(timer(int(nbytes), iters=20))
     payload = {
         "metric": "samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -218,7 +288,10 @@ def run_ours(args, rank, local_rank, world):
                                 "model state (params+grads+buckets ~134 MB) also exceeds L2",
                    "buckets": log.get("rebuilt_bucket_sizes") or log.get("initial_bucket_sizes")},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
-                   "reasons": clocks.get("reasons", [])},
+                   "reasons": clocks.get("reasons", []), "samples_in_region": 0 if clocks.get("pre_region_fallback")
+                   else clocks.get("samples", 0), "pre_region_fallback": bool(clocks.get("pre_region_fallback")),
+                   "source": clocks.get("source")},
+        "allreduce": allreduce,
         "e2e": {"value": samples / (e2e_ms / 1e3), "unit": "samples/s", "ms_per_step": e2e_ms / K,
                 "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,
                 "api": "DeviceLoader -> TrainStep(DDP(SimpleCNN), CrossEntropyLoss, SGD) -> loss.item()"},
@@ -237,9 +310,10 @@ def run_ours(args, rank, local_rank, world):
 # reference arm: unmodified dpp.py
 # =========================================================================================
 def run_reference(args, rank, local_rank, world):
-    ref_dir = os.path.join(ROOT, "baseline", "_ref")
-    if not os.path.exists(os.path.join(ref_dir, "dpp.py")):
-        emit(rank, {"impl": "reference", "unavailable": "baseline/_ref/dpp.py missing (reference not installed)"})
+    ref_dir = find_reference(rank, world)
+    if ref_dir is None:
+        emit(rank, {"impl": "reference", "unavailable": "dpp.py not found in baseline/_ref, $B200DDP_REFERENCE or "
+                                                        "/root/reference (run __graft_entry__.build() first)"})
         return
     try:
         import numpy as np
@@ -253,7 +327,7 @@ def run_reference(args, rank, local_rank, world):
     sys.path.insert(0, ref_dir)
     import dpp  # the unmodified reference module
 
-    from distributeddataparallel_b200.utils.clocks import ClockSampler
+    ClockSampler = load_clock_sampler()      # by path: none of this repository's native code is mapped here
 
     K, W, B = args.steps, args.warmup, BATCH
     need = (2 * (K + W) + 8) * B * world
@@ -303,7 +377,7 @@ def run_reference(args, rank, local_rank, world):
         def __iter__(self):
             it = iter(self.inner)
             ready = [next(it) for _ in range(K + W)]
-            marks["clock"] = ClockSampler(gpu_index=local_rank, period_ms=50).start()
+            marks["clock"] = ClockSampler(gpu_index=local_rank).start()
             for i, b in enumerate(ready):
                 if i == W:
                     self._sync()
@@ -316,6 +390,7 @@ def run_reference(args, rank, local_rank, world):
             marks["a1"].record()
             torch.cuda.synchronize()
             marks["clocks"] = marks["clock"].stop(marks.get("clock_mark", 0))
+            marks["a_loaded"] = loaded_native_libs()
             for i in range(K + W):
                 if i == W:
                     self._sync()
@@ -352,7 +427,10 @@ def run_reference(args, rank, local_rank, world):
                    "l2_policy": "fresh batch copied from host every step; model state ~134 MB exceeds L2",
                    "value_definition": "unmodified dpp.train loop fed batches collated beforehand"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
-                   "reasons": clocks.get("reasons", [])},
+                   "reasons": clocks.get("reasons", []), "samples_in_region": 0 if clocks.get("pre_region_fallback")
+                   else clocks.get("samples", 0), "pre_region_fallback": bool(clocks.get("pre_region_fallback")),
+                   "source": clocks.get("source")},
+        "repo_native_libs_loaded": marks.get("a_loaded", []),
         "e2e": {"value": samples / (b_ms / 1e3), "unit": "samples/s", "ms_per_step": b_ms / K,
                 "h2d_bytes_per_step": B * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 0,
                 "api": "dpp.train(rank, world_size) with its stock DataLoader (pageable H2D, loss.item() every 100 steps)"},

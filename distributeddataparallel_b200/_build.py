@@ -172,10 +172,60 @@ def build_host_extension(force: bool = False) -> Path:
     return HOST_EXT
 
 
+REF_DIR = ROOT / "baseline" / "_ref"
+
+
+def reference_sources() -> List[Path]:
+    """Places the unmodified reference script may be read from (first hit wins)."""
+    cands = []
+    if os.environ.get("B200DDP_REFERENCE"):
+        cands.append(Path(os.environ["B200DDP_REFERENCE"]))
+    cands.append(Path("/root/reference/dpp.py"))
+    return [c / "dpp.py" if c.is_dir() else c for c in cands]
+
+
+def install_reference(verbose: bool = False) -> Optional[Path]:
+    """Put the UNMODIFIED reference (``dpp.py``) under ``baseline/_ref`` so ``bench.py --impl reference``
+    finds it on the GPU box (the directory is git-ignored but travels with the snapshot).
+
+    The reference is a bare script: ``pip install --target baseline/_ref /root/reference`` refuses it
+    ("not installable": no setup.py / pyproject.toml).  It is therefore installed through pip from a
+    scratch copy carrying a minimal ``setup.py`` (``py_modules=["dpp"]``), and, if pip is unavailable,
+    copied.  Either way the result is compared byte for byte with the source.
+    """
+    dst = REF_DIR / "dpp.py"
+    src = next((c for c in reference_sources() if c.is_file()), None)
+    if src is None:
+        return dst if dst.is_file() else None
+    if dst.is_file() and dst.read_bytes() == src.read_bytes():
+        return dst
+    REF_DIR.mkdir(parents=True, exist_ok=True)
+    import tempfile
+
+    with tempfile.TemporaryDirectory(prefix="b200ddp_ref_") as tmp:
+        shutil.copyfile(src, Path(tmp) / "dpp.py")
+        (Path(tmp) / "setup.py").write_text(
+            "from setuptools import setup\nsetup(name='dpp-reference', version='0', py_modules=['dpp'])\n")
+        cmd = [sys.executable, "-m", "pip", "install", "--no-index", "--no-build-isolation", "--no-deps", "--quiet",
+               "--find-links", "/opt/wheelhouse", "--upgrade", "--target", str(REF_DIR), tmp]
+        proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if verbose or os.environ.get("B200DDP_BUILD_VERBOSE"):
+            print(f"[build] pip install reference -> rc {proc.returncode}", file=sys.stderr)
+    if not (dst.is_file() and dst.read_bytes() == src.read_bytes()):
+        shutil.copyfile(src, dst)                      # pip unavailable / refused: plain copy
+    if dst.read_bytes() != src.read_bytes():
+        raise RuntimeError(f"{dst} differs from {src}")
+    return dst
+
+
 def build_all(force: bool = False) -> None:
     build_host_extension(force)
     if kernel_sources():
         build_kernels(force)
+    try:
+        install_reference()
+    except Exception as e:  # the reference arm is a benchmark baseline, never a build blocker
+        print(f"[build] reference install skipped: {e}", file=sys.stderr)
 
 
 if __name__ == "__main__":

@@ -308,6 +308,44 @@ class P2PComm(CommBase):
                        bus_bandwidth_GBs=nbytes / (ms * 1e-3) * f / 1e9 if ms > 0 else 0.0)
         return out
 
+    def time_allreduce(self, nbytes: int, iters: int = 20, dtype: torch.dtype = torch.float32) -> dict:
+        """Collective: device time of one in-place all-reduce of ``nbytes`` (kernel picked as for a gradient
+        bucket), measured over ``iters`` back-to-back launches replayed from a CUDA graph, max over ranks.
+        Bus bandwidth uses the 2(N-1)/N convention of the BASELINE metric."""
+        arena = self._need_arena()
+        nbytes = -(-int(nbytes) // 16) * 16
+        self._ensure_staging()
+        if nbytes > self._staging_bytes:
+            return {"bytes": nbytes, "skipped": "larger than the staging region"}
+        off = self._staging
+        arena.memory[off:off + nbytes].zero_()
+        algo = self._pick_algo(nbytes)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self._allreduce_on(side, self.MAIN_CHANNEL, off, nbytes, dtype)
+            side.synchronize()
+            dist.barrier(group=self.group)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
+                for _ in range(iters):
+                    self._allreduce_on(side, self.MAIN_CHANNEL, off, nbytes, dtype)
+            graph.replay()
+            side.synchronize()
+            dist.barrier(group=self.group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(side)
+            graph.replay()
+            e1.record(side)
+            side.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        us = float(t.item()) * 1e3
+        f = 2 * (self.world_size - 1) / self.world_size
+        return {"bytes": nbytes, "us": round(us, 2), "bus_gbs": round(nbytes * f / (us * 1e-6) / 1e9, 1),
+                "algo": {1: "oneshot", 2: "twoshot", 3: "nvls"}[algo]}
+
     def all_reduce_avg_(self, flat: torch.Tensor) -> None:
         """In-place average on the current stream (tensor inside the arena, or staged through it)."""
         cur = torch.cuda.current_stream(self.device)
@@ -324,11 +362,14 @@ class P2PComm(CommBase):
             self._allreduce_on(cur, self.MAIN_CHANNEL, stage_off, nbytes, flat.dtype)
             view.copy_(stage)
 
-    def _staged_chunks(self, flat: torch.Tensor):
+    def _ensure_staging(self) -> None:
         arena = self._need_arena()
         if self._staging is None:
             self._staging_bytes = min(64 << 20, max(1 << 20, (arena.nbytes - arena._cursor) // 2))
             self._staging = arena.alloc(self._staging_bytes)
+
+    def _staged_chunks(self, flat: torch.Tensor):
+        self._ensure_staging()
         flat1 = flat.reshape(-1)
         esize = flat.element_size()
         per = self._staging_bytes // esize
