@@ -14,8 +14,15 @@
 //     wait                            <- ld.acquire.sys  >= epoch     dst spins on its own pad
 //
 // `epoch` is a per-(channel, block) counter kept in device memory and only ever incremented,
-// so flags are never reset (no reset race) and a CUDA graph can replay the kernels.  Spins are
-// bounded: a dead peer raises an error word instead of hanging the GPU.
+// so flags are never reset (no reset race) and a CUDA graph can replay the kernels; comparisons
+// are wrap-safe (signed difference), so the counters may roll over 2^32.
+//
+// Failure handling (the watchdog/abort a NCCL communicator brings with it).  A wait
+// is bounded by wall time (%globaltimer, `timeout_ns` in the context, 10 minutes by default like
+// the NCCL process-group timeout).  A block whose wait expires writes the error word (which the
+// host keeps in pinned, host-visible memory and polls every step), performs NONE of its loads /
+// stores of peer data, and overwrites its share of the LOCAL result with NaN: a collective that
+// did not complete can never pass for a completed one.
 //
 // Algorithms (S = message bytes, N = ranks, in place on the arena object):
 //   one-shot : barrier | every rank loads all N copies, sums in rank order 0..N-1 (bit-identical
@@ -26,6 +33,13 @@
 //              thread overwrites only what it has already read).  Per GPU and direction the links
 //              carry (N-1)/N*S of loads plus (N-1)/N*S of pushes, so t >= 2(N-1)/N * S / B_link,
 //              i.e. bus bandwidth S/t*2(N-1)/N is bounded by the link bandwidth.
+//   push     : small messages (<= 256 KB), ONE flag exchange: every rank stores its data into a
+//              per-source staging slot of every peer, releases a flag, waits for the N-1 peer flags
+//              and sums the staged copies in rank order (bit-identical everywhere).  Staging is
+//              double-buffered on the epoch parity, so no exit barrier is needed.
+//   wire16   : two-shot for fp32 buckets with a 16-bit wire format (bf16 / fp16 compress hooks):
+//              local cast fp32 -> 16 bit | barrier | owner pulls 16-bit slices, accumulates in fp32,
+//              pushes the 16-bit result | barrier | local cast back to fp32.  Half the NVLink bytes.
 //   broadcast: barrier | every rank pulls its 1/N slice from the root and pushes it to everyone |
 //              barrier (scatter + all-gather fused, root egress S instead of (N-1)*S).
 //
@@ -33,6 +47,7 @@
 // GPU, launched cooperatively so the spinning blocks are co-resident (the profiling guide
 // forbids mutually-waiting separate launches on one GPU).
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -44,7 +59,8 @@ namespace b200 {
 constexpr int kMaxRanks = 8;
 constexpr int kMaxCommBlocks = 128;          // flag rows per channel
 constexpr int kNumChannels = 4;              // independent flag/epoch sets (one per stream role)
-constexpr unsigned kSpinLimit = 400u * 1000u * 1000u;   // ~ tens of seconds of polling
+constexpr unsigned long long kDefaultTimeoutNs = 600ull * 1000ull * 1000ull * 1000ull;   // 10 min (NCCL PG default)
+constexpr size_t kPushMaxBytes = 256u << 10;   // per-source staging slot of the push all-reduce
 
 struct CommCtx {
   unsigned char* bufs[kMaxRanks];   // arena base of every rank, as mapped in THIS process
@@ -53,6 +69,7 @@ struct CommCtx {
   uint32_t* error;                  // local error word
   int rank, world, channel, emulate;
   unsigned char* mc;                // NVLS: multicast mapping of the arenas (0 if the box has none)
+  unsigned long long timeout_ns;    // bound on every wait (0: kDefaultTimeoutNs)
 };
 
 __device__ __forceinline__ int ctx_rank(const CommCtx& c) { return c.emulate ? (int)blockIdx.y : c.rank; }
@@ -61,8 +78,34 @@ __device__ __forceinline__ uint32_t* flag_slot(const CommCtx& c, int dst, int bl
   return c.flags[dst] + ((size_t)c.channel * kMaxCommBlocks + block) * kMaxRanks + src;
 }
 
-// All ranks' block `blockIdx.x` meet.  Acts as a system-scope release (before) / acquire (after).
-__device__ __forceinline__ void block_barrier(const CommCtx& c, int rank) {
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ void raise_error(const CommCtx& c, uint32_t code) {
+  // plain system-scope store: the word may live in pinned host memory (no PCIe atomics needed)
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(c.error), "r"(code) : "memory");
+  __threadfence_system();
+}
+
+// Spin until *flag >= epoch (wrap-safe) or the context's time bound expires.  false = timed out.
+__device__ __forceinline__ bool wait_flag(const CommCtx& c, const uint32_t* flag, uint32_t epoch, int peer) {
+  if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+  const unsigned long long limit = c.timeout_ns ? c.timeout_ns : kDefaultTimeoutNs;
+  const unsigned long long t0 = global_ns();
+  unsigned spins = 0;
+  while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+    if ((++spins & 63u) == 0 && global_ns() - t0 > limit) {
+      raise_error(c, 0xDEAD0000u | (uint32_t)peer);       // peer never arrived
+      return false;
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint32_t next_epoch(const CommCtx& c, int rank) {
   __shared__ uint32_t epoch_s;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -71,22 +114,32 @@ __device__ __forceinline__ void block_barrier(const CommCtx& c, int rank) {
     *e = epoch_s;
   }
   __syncthreads();
-  const uint32_t epoch = epoch_s;
+  return epoch_s;
+}
+
+// All ranks' block `blockIdx.x` meet.  Acts as a system-scope release (before) / acquire (after).
+// Returns false (uniformly over the block) when a peer did not arrive in time.
+__device__ __forceinline__ bool block_barrier(const CommCtx& c, int rank) {
+  __shared__ int ok_s;
+  const uint32_t epoch = next_epoch(c, rank);
+  if (threadIdx.x == 0) ok_s = 1;
+  __syncthreads();
   if ((int)threadIdx.x < c.world) {
     const int p = threadIdx.x;
     // st.release.sys is cumulative: it publishes this block's earlier peer stores (ordered
     // before it by the bar.sync above) without a separate fence round trip
     st_release_sys(flag_slot(c, p, blockIdx.x, rank), epoch);
-    const uint32_t* mine = flag_slot(c, rank, blockIdx.x, p);
-    unsigned spins = 0;
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-      if (++spins > kSpinLimit) {
-        atomicExch(c.error, 0xDEAD0000u | (uint32_t)p);   // peer p never arrived
-        break;
-      }
-    }
+    if (!wait_flag(c, flag_slot(c, rank, blockIdx.x, p), epoch, p)) ok_s = 0;
   }
   __syncthreads();
+  return ok_s != 0;
+}
+
+// A collective that cannot complete marks its share of the local result: NaN in every 16-byte vector.
+__device__ __forceinline__ void poison_local(const CommCtx& c, int rank, size_t offset, size_t nvec) {
+  const uint4 nan4 = make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);   // NaN as fp32 and as bf16 pairs
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (size_t)gridDim.x * blockDim.x)
+    *reinterpret_cast<uint4*>(c.bufs[rank] + offset + i * 16) = nan4;
 }
 
 // ---- 16-byte vector helpers ----------------------------------------------------------------
@@ -142,7 +195,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
                                                                 float scale) {
   constexpr int NMAX = NR ? NR : kMaxRanks;
   const int rank = ctx_rank(c), N = NR ? NR : c.world;
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
   const size_t trip = (size_t)gridDim.x * blockDim.x * U;
@@ -169,7 +222,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
         if (p < N) st_peer(c.bufs[p] + offset + i * 16, r);
     }
   }
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) poison_local(c, rank, offset, nvec);
 }
 
 // ---- NVLS (in-switch reduction through the NVLink multicast mapping) ---------------------------------
@@ -206,7 +259,7 @@ template <> struct Multimem<__nv_bfloat16> {
 template <typename T>
 __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommCtx c, size_t offset, size_t nvec, float scale) {
   const int rank = ctx_rank(c), N = c.world;
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
   constexpr int U = 4;
@@ -228,7 +281,7 @@ __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommCtx c, si
     }
   }
   __threadfence_system();
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) poison_local(c, rank, offset, nvec);
 }
 
 // ---- one-shot ------------------------------------------------------------------------------------
@@ -237,7 +290,7 @@ template <typename T>
 __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c, size_t offset, size_t nvec,
                                                                 float scale) {
   const int rank = ctx_rank(c), N = c.world;
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   uint4 res[kOneShotVecPerThread];
   const size_t base = (size_t)blockIdx.x * blockDim.x * kOneShotVecPerThread + threadIdx.x;
 #pragma unroll
@@ -255,7 +308,7 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c,
     }
     res[k] = Vec<T>::pack(a, scale);
   }
-  block_barrier(c, rank);                          // everyone has read everything: safe to overwrite
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);   // else: everyone has read everything
 #pragma unroll
   for (int k = 0; k < kOneShotVecPerThread; ++k) {
     const size_t i = base + (size_t)k * blockDim.x;
@@ -267,7 +320,10 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c,
 __global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t offset, size_t nvec, int root) {
   constexpr int U = 8;
   const int rank = ctx_rank(c), N = c.world;
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank)) {
+    if (rank != root) poison_local(c, rank, offset, nvec);
+    return;
+  }
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
   const size_t trip = (size_t)gridDim.x * blockDim.x * U;
@@ -287,10 +343,134 @@ __global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t 
         if (p < N && p != root) st_peer(c.bufs[p] + offset + i * 16, v[u]);
     }
   }
-  block_barrier(c, rank);
+  if (!block_barrier(c, rank) && rank != root) poison_local(c, rank, offset, nvec);
 }
 
 __global__ void __launch_bounds__(32) barrier_kernel(const CommCtx c) { block_barrier(c, ctx_rank(c)); }
+
+// ---- push all-reduce: one flag exchange, double-buffered staging ---------------------------------------
+// Staging object at `stage_off` in every arena: [parity 2][source rank kMaxRanks][kPushMaxBytes].  Block b owns
+// vectors [b*chunk, (b+1)*chunk) on EVERY rank, so block b's flag from peer p covers exactly the data block b reads.
+// Parity = epoch & 1 of this (channel, block): two pushes in a row alternate slots; if another collective ran on
+// the block in between, that collective's barrier already proves the peers are done with the previous push.
+constexpr int kPushVecPerThread = 4;
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_push_kernel(const CommCtx c, size_t offset, size_t nvec, float scale,
+                                                             size_t stage_off) {
+  __shared__ int ok_s;
+  const int rank = ctx_rank(c), N = c.world;
+  const uint32_t epoch = next_epoch(c, rank);
+  const size_t parity_off = stage_off + (size_t)(epoch & 1u) * kMaxRanks * kPushMaxBytes;
+  const size_t base = (size_t)blockIdx.x * blockDim.x * kPushVecPerThread + threadIdx.x;
+  uint4 mine[kPushVecPerThread];
+#pragma unroll
+  for (int k = 0; k < kPushVecPerThread; ++k) {
+    const size_t i = base + (size_t)k * blockDim.x;
+    if (i < nvec) {
+      mine[k] = *reinterpret_cast<const uint4*>(c.bufs[rank] + offset + i * 16);
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p)
+        if (p < N && p != rank) st_peer(c.bufs[p] + parity_off + (size_t)rank * kPushMaxBytes + i * 16, mine[k]);
+    }
+  }
+  if (threadIdx.x == 0) ok_s = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < N && (int)threadIdx.x != rank) {
+    const int p = threadIdx.x;
+    st_release_sys(flag_slot(c, p, blockIdx.x, rank), epoch);          // publishes the stores above (cumulative)
+    if (!wait_flag(c, flag_slot(c, rank, blockIdx.x, p), epoch, p)) ok_s = 0;
+  }
+  __syncthreads();
+  const bool ok = ok_s != 0;
+#pragma unroll
+  for (int k = 0; k < kPushVecPerThread; ++k) {
+    const size_t i = base + (size_t)k * blockDim.x;
+    if (i >= nvec) continue;
+    uint4 out = make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);
+    if (ok) {
+      float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int p = 0; p < kMaxRanks; ++p) {            // fixed order 0..N-1: same bits on every rank
+        if (p >= N) continue;
+        const uint4 v = p == rank ? mine[k]
+                                  : ld_peer(c.bufs[rank] + parity_off + (size_t)p * kPushMaxBytes + i * 16);
+        Vec<T>::acc(a, v);
+      }
+      out = Vec<T>::pack(a, scale);
+    }
+    *reinterpret_cast<uint4*>(c.bufs[rank] + offset + i * 16) = out;
+  }
+}
+
+// ---- two-shot with a 16-bit wire format for fp32 data ----------------------------------------------------
+// Unit of work: 8 floats = 32 bytes of fp32 = one 16-byte vector on the wire.  Staging object at `stage_off`:
+// [nw * 16 bytes].  W = __nv_bfloat16 or __half.
+template <typename W> struct Wire;
+template <> struct Wire<__nv_bfloat16> {
+  __device__ static uint32_t pack2(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  __device__ static float2 unpack2(uint32_t w) { return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)); }
+};
+template <> struct Wire<__half> {
+  __device__ static uint32_t pack2(float a, float b) {
+    const __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+  }
+  __device__ static float2 unpack2(uint32_t w) { return __half22float2(*reinterpret_cast<const __half2*>(&w)); }
+};
+
+template <typename W>
+__global__ void __launch_bounds__(512) allreduce_wire16_kernel(const CommCtx c, size_t offset, size_t nw, float scale,
+                                                               size_t stage_off) {
+  const int rank = ctx_rank(c), N = c.world;
+  const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float* data = reinterpret_cast<float*>(c.bufs[rank] + offset);
+  // 1. local cast into the staging object (pre-scaled by 1/world like the stock compress hooks: keeps fp16 in range)
+  for (size_t i = tid; i < nw; i += stride) {
+    const float4 lo = *reinterpret_cast<const float4*>(data + i * 8), hi = *reinterpret_cast<const float4*>(data + i * 8 + 4);
+    const uint4 w = make_uint4(Wire<W>::pack2(lo.x * scale, lo.y * scale), Wire<W>::pack2(lo.z * scale, lo.w * scale),
+                               Wire<W>::pack2(hi.x * scale, hi.y * scale), Wire<W>::pack2(hi.z * scale, hi.w * scale));
+    *reinterpret_cast<uint4*>(c.bufs[rank] + stage_off + i * 16) = w;
+  }
+  __threadfence_system();
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nw * 2);
+  // 2. owner of slice `rank`: pull the 16-bit slices, accumulate in fp32 in rank order, push the 16-bit result
+  const size_t per = (nw + N - 1) / N;
+  const size_t begin = min(nw, (size_t)rank * per), end = min(nw, begin + per);
+  for (size_t i = begin + tid; i < end; i += stride) {
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N) v[p] = ld_peer(c.bufs[p] + stage_off + i * 16);
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p) {
+      if (p >= N) continue;
+      const uint32_t w[4] = {v[p].x, v[p].y, v[p].z, v[p].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = Wire<W>::unpack2(w[j]);
+        a[2 * j] += f.x;
+        a[2 * j + 1] += f.y;
+      }
+    }
+    const uint4 r = make_uint4(Wire<W>::pack2(a[0], a[1]), Wire<W>::pack2(a[2], a[3]), Wire<W>::pack2(a[4], a[5]),
+                               Wire<W>::pack2(a[6], a[7]));
+#pragma unroll
+    for (int p = 0; p < kMaxRanks; ++p)
+      if (p < N) st_peer(c.bufs[p] + stage_off + i * 16, r);
+  }
+  if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nw * 2);
+  // 3. local cast back
+  for (size_t i = tid; i < nw; i += stride) {
+    const uint4 w = *reinterpret_cast<const uint4*>(c.bufs[rank] + stage_off + i * 16);
+    const float2 f0 = Wire<W>::unpack2(w.x), f1 = Wire<W>::unpack2(w.y), f2 = Wire<W>::unpack2(w.z), f3 = Wire<W>::unpack2(w.w);
+    *reinterpret_cast<float4*>(data + i * 8) = make_float4(f0.x, f0.y, f1.x, f1.y);
+    *reinterpret_cast<float4*>(data + i * 8 + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
+  }
+}
 
 template <typename K, typename... Args>
 static int launch_comm(K kernel, const CommCtx& c, int blocks, int threads, cudaStream_t st, Args... args) {
@@ -363,6 +543,39 @@ B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int d
   if (dtype == 0) { B200_TWOSHOT(float) }
   B200_TWOSHOT(__nv_bfloat16)
 #undef B200_TWOSHOT
+}
+
+B200_API size_t b200_allreduce_push_max_bytes(void) { return kPushMaxBytes; }
+B200_API size_t b200_allreduce_push_stage_bytes(void) { return (size_t)2 * kMaxRanks * kPushMaxBytes; }
+
+// Small-message all-reduce with a single flag exchange.  `stage_off`: arena offset of a staging object of
+// b200_allreduce_push_stage_bytes() bytes (same offset on every rank, used by one channel only).
+B200_API int b200_allreduce_push(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, size_t stage_off,
+                                 cudaStream_t stream) {
+  const CommCtx& c = *static_cast<const CommCtx*>(ctx);
+  if (nbytes % 16 != 0 || offset % 16 != 0 || stage_off % 16 != 0 || nbytes > kPushMaxBytes)
+    return static_cast<int>(cudaErrorInvalidValue);
+  const size_t nvec = nbytes / 16;
+  if (nvec == 0) return 0;
+  const size_t per_block = (size_t)512 * kPushVecPerThread;
+  const int blocks = (int)((nvec + per_block - 1) / per_block);
+  if (blocks > kMaxCommBlocks) return static_cast<int>(cudaErrorInvalidValue);
+  if (dtype == 0) return launch_comm(allreduce_push_kernel<float>, c, blocks, 512, stream, offset, nvec, scale, stage_off);
+  return launch_comm(allreduce_push_kernel<__nv_bfloat16>, c, blocks, 512, stream, offset, nvec, scale, stage_off);
+}
+
+// fp32 data, 16-bit wire (wire: 1 = bf16, 2 = fp16), fp32 accumulation.  `nbytes` % 32 == 0; the staging object at
+// `stage_off` needs nbytes / 2 bytes.
+B200_API int b200_allreduce_wire16(const void* ctx, size_t offset, size_t nbytes, int wire, float scale, size_t stage_off,
+                                   int max_blocks, cudaStream_t stream) {
+  const CommCtx& c = *static_cast<const CommCtx*>(ctx);
+  if (nbytes % 32 != 0 || offset % 16 != 0 || stage_off % 16 != 0 || (wire != 1 && wire != 2))
+    return static_cast<int>(cudaErrorInvalidValue);
+  const size_t nw = nbytes / 32;
+  if (nw == 0) return 0;
+  const int blocks = pick_blocks((nw + c.world - 1) / c.world, max(1, min(max_blocks, kMaxCommBlocks)));
+  if (wire == 1) return launch_comm(allreduce_wire16_kernel<__nv_bfloat16>, c, blocks, 512, stream, offset, nw, scale, stage_off);
+  return launch_comm(allreduce_wire16_kernel<__half>, c, blocks, 512, stream, offset, nw, scale, stage_off);
 }
 
 B200_API int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks,

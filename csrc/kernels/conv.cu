@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(NT) conv_gemm_kernel(const ConvArgs g) {
       for (int i = 0; i < 4; ++i) acc[i][j] += bj;
     }
   }
-  const bool vec_out = (g.N % 4 == 0) && (col0 + 3 < g.N);
+  const bool vec_out = (g.N % 4 == 0) && (col0 + 3 < g.N) && (reinterpret_cast<uintptr_t>(g.out) & 15u) == 0;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int row = row0 + i;

@@ -46,7 +46,15 @@ namespace b200 {
 namespace tc {
 
 constexpr int BM = 128;
-constexpr int STAGES = 4;
+// Ring depth per tile width.  128-wide tiles run 3 stages (96 KB) so that two CTAs -- e.g. a weight-gradient kernel
+// on a side stream next to the dgrad kernel of the following layer -- fit on one SM; the deep-layer convolutions this
+// kernel serves are latency bound, and 3 x 32 KB per CTA on ~128 CTAs already covers HBM latency x bandwidth.
+__host__ __device__ constexpr int stages_for(int bn) { return bn == 128 ? 3 : 4; }
+// dynamic shared memory: the operand ring, re-used by the epilogue as [BM][BN+1] staging + a [64][BN+1] reduced slice
+__host__ __device__ constexpr int smem_for(int bn) {
+  return (stages_for(bn) * (128 + bn) * 128 > (128 + 64) * (bn + 1) * 4 ? stages_for(bn) * (128 + bn) * 128
+                                                                        : (128 + 64) * (bn + 1) * 4) + 1024;
+}
 constexpr int PRODUCERS = 256;              // 8 warps
 constexpr int THREADS = PRODUCERS + 32;     // + MMA warp
 constexpr int ROW_BYTES = 128;              // bytes of K per tile row per stage (32 fp32 / 64 bf16)
@@ -331,6 +339,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   constexpr int KELEMS = ROW_BYTES / ES;            // per stage
   constexpr int UMMA_K = 32 / ES;                   // 8 (tf32) / 16 (bf16)
   constexpr int A_STAGE = BM * ROW_BYTES, B_STAGE = BN * ROW_BYTES;
+  constexpr int STAGES = stages_for(BN);
   constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;          // 32 / 64 / 128 / 256: powers of two
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar, cl_ready, cl_done;
@@ -1291,7 +1300,7 @@ static bool make_im2col_map(CUtensorMap* m, const void* x, bool bf16, const Geom
 
 template <int AK, int BK_, int BN, bool BF16>
 static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
-  constexpr int smem = STAGES * (BM + BN) * ROW_BYTES + 1024;
+  constexpr int smem = smem_for(BN);
   constexpr int KELEMS = ROW_BYTES / (BF16 ? 2 : 4);
   Args a = a_in;
   CUtensorMap map_a{}, map_b{};

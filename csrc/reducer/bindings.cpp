@@ -1,5 +1,6 @@
 // pybind surface of the native host runtime (module name: distributeddataparallel_b200._C).
 #include "reducer.h"
+#include "vmm_arena.h"
 
 namespace py = pybind11;
 using b200ddp::Reducer;
@@ -37,6 +38,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("attach_hooks", &Reducer::attach_hooks)
       .def("num_buckets", &Reducer::num_buckets)
       .def("bucket_sizes", &Reducer::bucket_sizes)
+      .def("set_tail_splits", &Reducer::set_tail_splits)
+      .def("launch_unit_sizes", &Reducer::launch_unit_sizes)
+      .def("num_logical_buckets", &Reducer::num_logical_buckets)
       .def("bucket_params", &Reducer::bucket_params)
       .def("bucket_flat", &Reducer::bucket_flat)
       .def("grad_slot", &Reducer::grad_slot)
@@ -47,4 +51,22 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("_autograd_hook", &Reducer::autograd_hook, release())
       .def("shadow_backward", &Reducer::shadow_backward, release())
       .def("_finalize_backward", &Reducer::finalize_backward, release());
+
+  // Symmetric arena on the CUDA VMM API + NVLink multicast (csrc/runtime/vmm_arena.h).  Stages return "" or a message.
+  using b200ddp::VmmArena;
+  py::class_<VmmArena, std::shared_ptr<VmmArena>>(m, "VmmArena")
+      .def(py::init<int, size_t, int, int, std::string>(), py::arg("device"), py::arg("nbytes"), py::arg("rank"),
+           py::arg("world"), py::arg("session"))
+      .def("alloc_local", &VmmArena::alloc_local, release())
+      .def("exchange", &VmmArena::exchange, release())
+      .def("map_peers", &VmmArena::map_peers, release())
+      .def("multicast_create", &VmmArena::multicast_create, release())
+      .def("multicast_bind", &VmmArena::multicast_bind, release())
+      .def("close", &VmmArena::close, release())
+      .def("multicast_supported", &VmmArena::multicast_supported)
+      .def("base", &VmmArena::base)
+      .def("peer_base", &VmmArena::peer_base)
+      .def("multicast_base", &VmmArena::multicast_base)
+      .def("nbytes", &VmmArena::nbytes)
+      .def("granularity", &VmmArena::granularity);
 }

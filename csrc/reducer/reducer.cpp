@@ -253,7 +253,21 @@ void Reducer::detach_hooks() {
   accumulator_index_.clear();
 }
 
-void Reducer::build_buckets(const std::vector<std::vector<int64_t>>& bucket_indices) {
+void Reducer::set_tail_splits(std::vector<int64_t> thresholds) {
+  std::lock_guard<std::mutex> lock(mu_);
+  std::sort(thresholds.begin(), thresholds.end(), std::greater<int64_t>());
+  thresholds.erase(std::remove_if(thresholds.begin(), thresholds.end(), [](int64_t v) { return v <= 0; }), thresholds.end());
+  tail_splits_ = std::move(thresholds);
+}
+
+std::vector<int64_t> Reducer::launch_unit_sizes() const {
+  std::vector<int64_t> out;
+  for (const auto& b : buckets_) out.push_back(b.payload_bytes);
+  return out;
+}
+
+void Reducer::build_buckets(const std::vector<std::vector<int64_t>>& bucket_indices,
+                            const std::vector<int64_t>& logical_of_unit) {
   py::gil_scoped_acquire gil;
   at::NoGradGuard no_grad;
   std::vector<uint8_t> seen(params_.size(), 0);
@@ -263,6 +277,9 @@ void Reducer::build_buckets(const std::vector<std::vector<int64_t>>& bucket_indi
     const auto& members = bucket_indices[bi];
     TORCH_CHECK(!members.empty(), "empty bucket");
     Bucket b;
+    b.logical = logical_of_unit.empty() ? static_cast<int64_t>(bi) : logical_of_unit.at(bi);
+    b.closes_logical = bi + 1 == bucket_indices.size() || logical_of_unit.empty() ||
+                       logical_of_unit.at(bi + 1) != b.logical;
     const auto& first = params_.at(members[0]);
     const int64_t esize = static_cast<int64_t>(first.element_size());
     const int64_t align = std::max<int64_t>(1, kSlotAlignBytes / esize);
@@ -312,6 +329,11 @@ void Reducer::build_buckets(const std::vector<std::vector<int64_t>>& bucket_indi
     }
   }
   buckets_ = std::move(fresh);
+  logical_sizes_.clear();
+  for (const auto& b : buckets_) {
+    if (static_cast<int64_t>(logical_sizes_.size()) <= b.logical) logical_sizes_.resize(b.logical + 1, 0);
+    logical_sizes_[b.logical] += b.payload_bytes;
+  }
   reset_round();
 }
 
@@ -426,7 +448,7 @@ void Reducer::launch_ready_buckets() {
     }
     b.launched = true;
     ++next_bucket_;
-    ++num_buckets_reduced_total_;
+    if (b.closes_logical) ++num_buckets_reduced_total_;
   }
 }
 
@@ -530,17 +552,41 @@ std::vector<std::vector<int64_t>> Reducer::rebuild_buckets(const std::vector<int
   ordered.reserve(order.size());
   for (int64_t i : order) ordered.push_back(params_.at(i));
   auto assignment = compute_bucket_assignment_by_size(ordered, {first_bucket_bytes_, bucket_bytes_cap_}, order);
-  build_buckets(assignment.first);
+  // launch units: the stock buckets, with the last one cut at the tail thresholds
+  std::vector<std::vector<int64_t>> units;
+  std::vector<int64_t> logical;
+  for (size_t bi = 0; bi < assignment.first.size(); ++bi) {
+    const auto& members = assignment.first[bi];
+    if (bi + 1 != assignment.first.size() || tail_splits_.empty() || members.size() < 2) {
+      units.push_back(members);
+      logical.push_back(static_cast<int64_t>(bi));
+      continue;
+    }
+    std::vector<int64_t> suffix(members.size() + 1, 0);       // bytes from member k to the end
+    for (int64_t k = static_cast<int64_t>(members.size()) - 1; k >= 0; --k) {
+      const auto& p = params_.at(members[k]);
+      suffix[k] = suffix[k + 1] + p.numel() * static_cast<int64_t>(p.element_size());
+    }
+    size_t begin = 0;
+    for (int64_t thr : tail_splits_) {
+      size_t cut = begin;
+      while (cut < members.size() && suffix[cut] > thr) ++cut;   // first member from which the rest fits under thr
+      if (cut > begin && cut < members.size()) {
+        units.emplace_back(members.begin() + begin, members.begin() + cut);
+        logical.push_back(static_cast<int64_t>(bi));
+        begin = cut;
+      }
+    }
+    units.emplace_back(members.begin() + begin, members.end());
+    logical.push_back(static_cast<int64_t>(bi));
+  }
+  build_buckets(units, logical);
   has_rebuilt_ = true;
   ready_order_.clear();
   return assignment.first;
 }
 
-std::vector<int64_t> Reducer::bucket_sizes() const {
-  std::vector<int64_t> out;
-  for (const auto& b : buckets_) out.push_back(b.payload_bytes);
-  return out;
-}
+std::vector<int64_t> Reducer::bucket_sizes() const { return logical_sizes_; }
 
 std::vector<std::vector<int64_t>> Reducer::bucket_params() const {
   std::vector<std::vector<int64_t>> out;
@@ -569,7 +615,7 @@ py::dict Reducer::logging_data() const {
     std::lock_guard<std::mutex> lock(mu_);
     for (const auto& p : params_) s.total += p.numel() * static_cast<int64_t>(p.element_size());
     s.sizes = bucket_sizes();
-    s.nb = num_buckets();
+    s.nb = num_logical_buckets();
     s.reduced = num_buckets_reduced_total_;
     s.iters = iterations_;
     s.alias = alias_hits_;
@@ -589,6 +635,7 @@ py::dict Reducer::logging_data() const {
   d["first_bucket_bytes"] = first_bucket_bytes_;
   d["has_rebuilt_buckets"] = s.rebuilt;
   d["num_buckets"] = s.nb;
+  d["launch_unit_sizes"] = launch_unit_sizes();
   d["num_buckets_reduced"] = s.reduced;
   d["iteration"] = s.iters;
   d["world_size"] = world_size_;

@@ -66,6 +66,8 @@ struct Bucket {
   at::Tensor flat;
   int64_t numel = 0;               // padded element count of `flat`
   int64_t payload_bytes = 0;       // sum of param bytes (what the logger reports)
+  int64_t logical = -1;            // index of the stock-layout bucket this launch unit belongs to
+  bool closes_logical = true;      // last unit of its logical bucket
   int64_t pending = 0;
   bool launched = false;
   py::object handle;               // what comm.launch returned
@@ -86,6 +88,12 @@ class Reducer {
   std::vector<int64_t> rebuild_order() const { return ready_order_; }
   // Apply rank 0's order; returns the new per-bucket parameter lists.
   std::vector<std::vector<int64_t>> rebuild_buckets(const std::vector<int64_t>& order);
+  // Stream the LAST bucket: thresholds in bytes measured from the end of the bucket (e.g. {1 MiB, 64 KiB}).  The
+  // bucket is cut where the gradients still to come fit under each threshold, and every piece is reduced as soon as
+  // its own gradients are ready -- so only the final few KB (the stem's weight gradient) are left after backward ends.
+  // The reported layout (bucket_sizes, logging) stays the stock one.  Takes effect at the next rebuild.
+  void set_tail_splits(std::vector<int64_t> thresholds);
+  std::vector<int64_t> launch_unit_sizes() const;
   void set_require_sync(bool v) { require_sync_ = v; }
   bool require_sync() const { return require_sync_; }
   void set_comm(py::object comm) { comm_ = std::move(comm); }
@@ -106,7 +114,8 @@ class Reducer {
   int64_t iterations() const { return iterations_; }
   bool has_rebuilt() const { return has_rebuilt_; }
   // Replay bookkeeping when a captured CUDA graph re-runs a step without the hooks firing.
-  void note_graph_replay() { ++iterations_; ++num_buckets_reduced_total_; }
+  void note_graph_replay() { ++iterations_; num_buckets_reduced_total_ += num_logical_buckets(); }
+  int64_t num_logical_buckets() const { return static_cast<int64_t>(logical_sizes_.size()); }
 
   // test hooks
   void autograd_hook(int64_t index);
@@ -116,7 +125,8 @@ class Reducer {
   void shadow_backward();
 
  private:
-  void build_buckets(const std::vector<std::vector<int64_t>>& bucket_indices);
+  void build_buckets(const std::vector<std::vector<int64_t>>& bucket_indices,
+                     const std::vector<int64_t>& logical_of_unit = {});
   void mark_variable_ready(int64_t index);
   void launch_ready_buckets();
   void search_unused(const std::vector<at::Tensor>& outputs);
@@ -133,6 +143,8 @@ class Reducer {
   bool find_unused_;
   int64_t first_bucket_bytes_;
   int64_t bucket_bytes_cap_;
+  std::vector<int64_t> tail_splits_;       // descending byte thresholds for streaming the last bucket
+  std::vector<int64_t> logical_sizes_;     // payload bytes per stock-layout bucket
 
   std::vector<std::shared_ptr<torch::autograd::Node>> accumulators_;
   std::vector<uintptr_t> hook_keys_;

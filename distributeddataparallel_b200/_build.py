@@ -166,7 +166,7 @@ def build_host_extension(force: bool = False) -> Path:
         _stamp(o, sd)
     torch_lib = Path(torch.__file__).parent / "lib"
     link = [cxx, "-shared", "-o", str(HOST_EXT), *map(str, objs), f"-L{torch_lib}", "-lc10", "-ltorch_cpu",
-            "-ltorch", "-ltorch_python", f"-Wl,-rpath,{torch_lib}"]
+            "-ltorch", "-ltorch_python", "-ldl", f"-Wl,-rpath,{torch_lib}"]
     _run(link, objdir / "link.log")
     _stamp(HOST_EXT, digest)
     return HOST_EXT

@@ -39,7 +39,7 @@ class TrainConfig:
     optimizer: str = "sgd"             # sgd | adam
     bucket_cap_mb: float = 25.0        # stock DDP default
     first_bucket_mb: float = 1.0
-    allreduce_algo: str = "auto"       # auto | oneshot | twoshot | nvls | nccl
+    allreduce_algo: str = "auto"       # auto | oneshot | twoshot | nvls | push  (P2P data plane; NCCL is --comm c10d)
     comm: str = "auto"                 # auto | p2p (own NVLink kernels) | c10d (NCCL/gloo baseline)
     cuda_graph: bool = True            # capture the whole step once shapes/buckets are final
     native_ops: bool = True            # route model math through the sm_100a kernels
@@ -111,7 +111,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--dtype", default=d.dtype, choices=["fp32", "bf16"])
     p.add_argument("--bucket-cap-mb", type=float, default=d.bucket_cap_mb)
     p.add_argument("--allreduce-algo", default=d.allreduce_algo,
-                   choices=["auto", "oneshot", "twoshot", "nvls", "nccl"])
+                   choices=["auto", "oneshot", "twoshot", "nvls", "push"])
     p.add_argument("--comm", default=d.comm, choices=["auto", "p2p", "c10d"])
     p.add_argument("--max-steps", type=int, default=None)
     p.add_argument("--checkpoint-path", default=None)

@@ -12,8 +12,14 @@ bucket all-reduces on the side stream, and the fused optimizer update -- into on
 graph and replays it.  Hooks run at capture time only; what is replayed is the kernel
 DAG they produced, including the fork/join onto the communication stream.
 
-A batch whose shape differs from the captured one (the ragged last batch of an epoch,
-SURVEY §3.4) runs eagerly.
+Shapes: the steady-state batch is captured first; a second shape -- the ragged last batch of
+an epoch (dpp.py:35 keeps ``drop_last=False``: 16 / 8 / 20 / 10 samples at 1 / 2 / 4 / 8 ranks,
+SURVEY §3.4), identical on every rank -- runs eagerly the first time it is seen (the
+convolution tuner needs one eager pass per new geometry) and is captured the second time, up
+to ``max_graphs`` graphs (``B200DDP_MAX_GRAPHS``, default 2).
+
+After every step the DDP wrapper's health word (pinned host memory, written by a collective
+kernel whose peer never arrived) is read; a set word raises on this rank.
 """
 from __future__ import annotations
 
@@ -34,11 +40,13 @@ class TrainStep:
         self.replays = 0
         self.eager_steps = 0
         self._graphs: Dict[Tuple, dict] = {}
+        self._seen: Dict[Tuple, int] = {}
         dev = next(model.parameters()).device
         self.use_graph = bool(cuda_graph) and dev.type == "cuda"
         self._ddp = model if hasattr(model, "reducer") else None
         import os
 
+        self.max_graphs = int(os.environ.get("B200DDP_MAX_GRAPHS", "2"))
         self._nvtx = dev.type == "cuda" and os.environ.get("B200DDP_NVTX", "0") != "0"
 
     def _forward_loss(self, data, target):
@@ -79,8 +87,14 @@ class TrainStep:
         static_x = data.clone(memory_format=torch.preserve_format)
         static_y = target.clone()
         self.optimizer.zero_grad(set_to_none=True)
-        torch.cuda.synchronize()
         from .ops import native
+
+        native.join_side_streams()
+        native.save_choices()
+        torch.cuda.synchronize()
+        comm = getattr(self._ddp, "comm", None)
+        if comm is not None and getattr(comm, "_ahead_event", None) is not None:
+            comm._ahead_event = None       # everything issued so far is complete: nothing to wait for inside the capture
 
         launches0 = native.launch_count()
         graph = torch.cuda.CUDAGraph()
@@ -102,6 +116,8 @@ class TrainStep:
         finally:
             if self._ddp is not None:
                 self._ddp.reducer.attach_hooks()
+            if comm is not None and getattr(comm, "_ahead_event", None) is not None:
+                comm._ahead_event = None   # recorded inside the capture: the graph's own join orders later work
         native.set_launches_per_capture(native.launch_count() - launches0)
         entry = {"graph": graph, "x": static_x, "y": static_y, "loss": loss.detach()}
         return entry
@@ -109,22 +125,37 @@ class TrainStep:
     def __call__(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         self.steps += 1
         if not self.use_graph or not self.model.training or (self._ddp is not None and self._ddp._join_enabled):
-            return self._eager(data, target)         # join(): every iteration carries a control collective
+            loss = self._eager(data, target)         # join(): every iteration carries a control collective
+            self._health()
+            return loss
         key = (tuple(data.shape), data.dtype, tuple(target.shape))
         entry = self._graphs.get(key)
         if entry is None:
-            if not self._ready_for_capture() or len(self._graphs) >= 1:
-                # only the steady-state shape is captured; other shapes (ragged tail) stay eager
-                return self._eager(data, target)
+            seen = self._seen.get(key, 0)
+            self._seen[key] = seen + 1
+            # a shape other than the first captured one (ragged tail) gets one eager pass first
+            first_pass = bool(self._graphs) and seen == 0
+            if not self._ready_for_capture() or len(self._graphs) >= self.max_graphs or first_pass:
+                loss = self._eager(data, target)
+                self._health()
+                return loss
             entry = self._graphs[key] = self._capture(data, target)
             # the capture itself does not execute the step: fall through to a replay
+        sync_hyper = getattr(self.optimizer, "sync_hyper", None)
+        if sync_hyper is not None:
+            sync_hyper()                 # the captured update reads lr & co. from device memory: refresh if changed
         entry["x"].copy_(data, non_blocking=True)
         entry["y"].copy_(target, non_blocking=True)
         entry["graph"].replay()
         self.replays += 1
         if self._ddp is not None:
             self._ddp.reducer.note_graph_replay()
+            self._health()
         return entry["loss"]
+
+    def _health(self) -> None:
+        if self._ddp is not None:
+            self._ddp.check_health(sync=False)
 
     def load_inputs_and_replay(self, entry_key=None) -> torch.Tensor:
         """Replay on whatever is already in the static input buffers (bench helper)."""

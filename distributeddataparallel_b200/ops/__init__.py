@@ -109,26 +109,40 @@ def cross_entropy(logits, target):
     return F.cross_entropy(logits, target)
 
 
+def _nat_tf():
+    from . import native_tf
+
+    return native_tf
+
+
 def layer_norm(x, weight, bias, eps=1e-5):
+    """LayerNorm over the last dimension (GPT-2 blocks); hand-written kernel on CUDA (ops/native_tf.py)."""
     if use_native(x):
-        return _nat().layer_norm(x, weight, bias, eps)
+        return _nat_tf().layer_norm(x, weight, bias, eps)
     return F.layer_norm(x, (x.shape[-1],), weight, bias, eps)
 
 
 def gelu(x):
+    """tanh-approximated GELU, the GPT-2 activation."""
     if use_native(x):
-        return _nat().gelu(x)
+        return _nat_tf().gelu(x)
     return F.gelu(x, approximate="tanh")
 
 
-def causal_attention(q, k, v):
-    """q,k,v: [B, H, T, D] -> [B, H, T, D], causal softmax(QK^T/sqrt(D))V."""
-    if use_native(q):
-        return _nat().causal_attention(q, k, v)
-    return F.scaled_dot_product_attention(q, k, v, is_causal=True)
+def causal_self_attention(qkv, heads: int):
+    """qkv: [B, T, 3*D] fused projection output -> [B, T, D]; causal softmax(QK^T/sqrt(d))V per head.  On CUDA the
+    fused tcgen05 attention kernel (csrc/kernels/attention_tcgen05.cu) reads Q, K, V in place."""
+    if use_native(qkv):
+        return _nat_tf().causal_self_attention(qkv, heads)
+    b, t, d3 = qkv.shape
+    d = d3 // 3
+    q, k, v = (z.view(b, t, heads, d // heads).transpose(1, 2) for z in qkv.split(d, dim=2))
+    y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return y.transpose(1, 2).reshape(b, t, d)
 
 
-def embedding(idx, weight):
-    if use_native(weight):
-        return _nat().embedding(idx, weight)
-    return F.embedding(idx, weight)
+def embedding(idx, wte, wpe):
+    """Token + position embedding: wte[idx] + wpe[0:T]."""
+    if use_native(wte):
+        return _nat_tf().embedding(idx, wte, wpe)
+    return F.embedding(idx, wte) + wpe[: idx.shape[1]]

@@ -106,20 +106,116 @@ class _Scratch:
         self.red_ticket = torch.zeros(4, dtype=torch.int32, device=device)
 
 
-_scratch: Dict[int, _Scratch] = {}
+_scratch: Dict[tuple, _Scratch] = {}
+_lane = 0          # 0: the caller's stream; 1..: a weight-gradient side stream (each lane has its own split-K scratch)
 
 
 def scratch(device: torch.device) -> _Scratch:
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    s = _scratch.get(idx)
+    s = _scratch.get((idx, _lane))
     if s is None:
-        s = _scratch[idx] = _Scratch(torch.device("cuda", idx))
+        s = _scratch[(idx, _lane)] = _Scratch(torch.device("cuda", idx))
     return s
 
 
 def _ws_args(dev: torch.device):
     s = scratch(dev)
     return (_ptr(s.workspace), _sz(s.WORKSPACE_BYTES), _ptr(s.counters), _i(s.MAX_COUNTERS))
+
+
+# ---------------------------------------------------------------------------------------
+# weight-gradient side streams
+# ---------------------------------------------------------------------------------------
+# Nothing downstream in the backward pass consumes a weight gradient: only the bucket reduction and the
+# optimizer do.  The deep layers of the dpp.py model are latency-bound kernels that leave most SMs idle, so
+# wgrad kernels are issued on side streams and run UNDER the dgrad / BatchNorm-backward chain of the following
+# layers (the fork/join is captured in the step graph like any other cross-stream edge).  Ordering:
+#   * fork: the side stream waits for an event recorded on the caller's stream (dY and x are ready);
+#   * every consumer joins: the reducer's bucket launch (parallel/p2p.py, comm.py), the end-of-backward
+#     callback queued on the autograd engine, and the fused optimizers.
+# Tensors read on a side stream are ``record_stream``-ed so the caching allocator does not recycle them early.
+_SIDE_STREAMS = int(os.environ.get("B200DDP_WGRAD_STREAMS", "1"))
+_side: Dict[int, list] = {}          # device index -> [streams]
+_side_next: Dict[int, int] = {}
+_side_dirty: Dict[int, set] = {}     # device index -> lanes with work the caller's stream has not joined yet
+_join_queued = False
+
+
+def set_wgrad_streams(n: int) -> None:
+    """0 disables the side streams (weight gradients run in line on the caller's stream)."""
+    global _SIDE_STREAMS
+    _SIDE_STREAMS = max(0, int(n))
+
+
+def _side_stream(dev: torch.device):
+    """(lane, stream) of the next weight-gradient side stream, or (0, None) when disabled."""
+    if _SIDE_STREAMS <= 0:
+        return 0, None
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    pool = _side.get(idx)
+    if pool is None or len(pool) != _SIDE_STREAMS:
+        pool = _side[idx] = [torch.cuda.Stream(device=idx) for _ in range(_SIDE_STREAMS)]
+    k = _side_next.get(idx, 0) % len(pool)
+    _side_next[idx] = k + 1
+    return k + 1, pool[k]
+
+
+def side_stream_events(device=None):
+    """One fresh event per side stream that has un-joined work: whoever consumes weight gradients on another
+    stream (the bucket all-reduce on the communication stream) waits on these."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    out = []
+    for lane in sorted(_side_dirty.get(idx, ())):
+        ev = torch.cuda.Event()
+        ev.record(_side[idx][lane - 1])
+        out.append(ev)
+    return out
+
+
+def join_side_streams(device=None) -> None:
+    """Order the current stream after all outstanding side-stream work."""
+    idx = torch.cuda.current_device() if device is None else torch.device(device).index
+    cur = torch.cuda.current_stream(idx)
+    for ev in side_stream_events(idx):
+        cur.wait_event(ev)
+    _side_dirty.pop(idx, None)
+
+
+def _end_of_backward_join() -> None:
+    global _join_queued
+    _join_queued = False
+    for idx in list(_side_dirty):
+        join_side_streams(idx)
+
+
+def _run_on_side(dev: torch.device, tensors, fn) -> None:
+    """Run ``fn()`` (kernel launches) on a side stream forked from the current one."""
+    global _lane, _join_queued
+    lane, stream = _side_stream(dev)
+    if stream is None:
+        fn()
+        return
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(idx))
+    stream.wait_event(ev)
+    prev = _lane
+    _lane = lane
+    try:
+        with torch.cuda.stream(stream):
+            fn()
+    finally:
+        _lane = prev
+    for t in tensors:
+        if t is not None:
+            t.record_stream(stream)
+    _side_dirty.setdefault(idx, set()).add(lane)
+    if not _join_queued:
+        try:
+            torch.autograd.Variable._execution_engine.queue_callback(_end_of_backward_join)
+            _join_queued = True
+        except RuntimeError:
+            join_side_streams(idx)       # not inside a backward pass: join right away
 
 
 # ---------------------------------------------------------------------------------------
@@ -147,6 +243,96 @@ def tensor_cores_enabled() -> bool:
 
 def conv_choices() -> Dict[tuple, int]:
     return dict(_choice)
+
+
+# ---- tuned choices: persisted per GPU model, identical on every rank ------------------------------------------------
+# The table maps (entry point, geometry) -> kernel variant.  It is loaded from ``tuning/<gpu name>.json`` next to the
+# package (shipped with the repository for B200, extended on the fly for new shapes), so tests, ``smoke()`` and
+# training runs do not re-time known shapes, and every rank of a job runs the same variants -- per-rank timing noise
+# can no longer make ranks round differently.  ``B200DDP_TUNE=retune`` ignores the file; ``=off`` never writes it.
+_TUNE_MODE = os.environ.get("B200DDP_TUNE", "auto")
+_tune_loaded = False
+_tune_dirty = False
+
+
+def _tune_path():
+    from pathlib import Path
+
+    name = "".join(ch if ch.isalnum() else "_" for ch in torch.cuda.get_device_name())
+    return Path(__file__).resolve().parent.parent / "tuning" / f"{name}.json"
+
+
+def _key_str(key: tuple) -> str:
+    return key[0] + "|" + ",".join(str(v) for v in key[1:])
+
+
+def _key_from(s: str) -> tuple:
+    name, rest = s.split("|", 1)
+    return (name,) + tuple(int(v) for v in rest.split(",") if v != "")
+
+
+def _load_choices() -> None:
+    global _tune_loaded
+    if _tune_loaded:
+        return
+    _tune_loaded = True
+    if _TUNE_MODE == "retune" or os.environ.get("B200DDP_TC_VARIANTS"):
+        return
+    import json
+
+    try:
+        table = json.loads(_tune_path().read_text())
+    except (OSError, ValueError):
+        return
+    for k, v in table.get("choices", {}).items():
+        _choice.setdefault(_key_from(k), int(v))
+
+
+def save_choices(force: bool = False) -> None:
+    """Write the table (atomic rename); only local rank 0 writes, and only when something new was tuned."""
+    global _tune_dirty
+    if not (_tune_dirty or force) or _TUNE_MODE == "off" or os.environ.get("B200DDP_TC_VARIANTS"):
+        return
+    if int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", "0")) or 0) != 0:
+        return
+    import json
+
+    path = _tune_path()
+    try:
+        path.parent.mkdir(parents=True, exist_ok=True)
+        body = {"gpu": torch.cuda.get_device_name(), "format": 1,
+                "choices": {_key_str(k): v for k, v in sorted(_choice.items(), key=lambda kv: _key_str(kv[0]))}}
+        tmp = path.with_suffix(f".tmp{os.getpid()}")
+        tmp.write_text(json.dumps(body, indent=0, sort_keys=True))
+        os.replace(tmp, path)
+        _tune_dirty = False
+    except OSError:
+        pass
+
+
+def sync_choices(group=None) -> None:
+    """Collective: all ranks end up with the same table -- the union of what any rank tuned, the lowest rank winning
+    where two ranks timed the same shape differently."""
+    import torch.distributed as dist
+
+    global _tune_dirty
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    tables = [None] * dist.get_world_size(group)
+    dist.all_gather_object(tables, {_key_str(k): v for k, v in _choice.items()}, group=group)
+    merged = {}
+    for t in reversed(tables):          # lowest rank wins on conflicts
+        merged.update(t)
+    before = dict(_choice)
+    _choice.clear()
+    _choice.update({_key_from(k): int(v) for k, v in merged.items()})
+    if _choice != before or dist.get_rank(group) == 0:
+        _tune_dirty = _tune_dirty or _choice != before
+
+
+import atexit as _atexit
+
+_atexit.register(save_choices)
 
 
 # split-K variants the tuner tries for a tcgen05 convolution: (upper bound on the split factor, reduce the splits
@@ -220,9 +406,10 @@ def _time_variant(fn, acts=(), iters: int = 6) -> float:
 
 def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device, acts=()) -> None:
     """Dispatch one convolution pass to the tcgen05 kernel (with a tuned split-K bound) or to the FFMA kernel."""
-    global _launches, tc_launches, ffma_launches
+    global _launches, tc_launches, ffma_launches, _tune_dirty
     choice = 32 if _tc_mode == "1" else 0          # 0 = FFMA, otherwise the split-K cap of the tcgen05 call
     if _tc_mode == "auto":
+        _load_choices()
         key = (name,) + tuple(g.value for g in geom)
         choice = _choice.get(key)
         if choice is None:
@@ -243,6 +430,7 @@ def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device, acts=()) 
                         if t < best:
                             best, choice = t, v
                 _choice[key] = choice
+                _tune_dirty = True
     if choice:
         rc = _launch_tc(name, head, geom, dev, choice)
         if rc == 0:
@@ -260,7 +448,12 @@ def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device, acts=()) 
 
 def tc_error_word(device=None) -> int:
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-    return int(scratch(dev).error[0].item()) & 0xFFFFFFFF
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    word = 0
+    for (d, _lane_id), s in list(_scratch.items()):          # every lane (caller's stream + side streams)
+        if d == idx:
+            word |= int(s.error[0].item()) & 0xFFFFFFFF
+    return word
 
 
 def gemm_tc(a: torch.Tensor, b: torch.Tensor, mode: int, bias: Optional[torch.Tensor] = None,
@@ -297,7 +490,12 @@ def _empty_nhwc(n, c, h, w, device) -> torch.Tensor:
 
 def _grad_target(param: torch.Tensor, slot: Optional[torch.Tensor], like: torch.Tensor):
     """(tensor to write the gradient into, accumulate?)  Prefer the DDP bucket slot."""
-    if slot is not None and param.grad is None and slot.shape == like.shape:
+    # A parameter used by two ops in one forward (a shared layer) reaches here twice with ``grad is None`` --
+    # AccumulateGrad only runs after both contributions exist -- so the slot is handed out once per backward
+    # pass (the DDP wrapper clears the claim in forward); later uses get private memory and autograd adds them up.
+    if slot is not None and param.grad is None and slot.shape == like.shape and not getattr(param, "_slot_claimed", False):
+        if hasattr(param, "_ddp_index"):
+            param._slot_claimed = True
         return slot.detach(), False          # fresh alias of the slot: AccumulateGrad adopts it
     return torch.empty_like(like, memory_format=torch.preserve_format), False
 
@@ -370,7 +568,14 @@ class _Conv2d(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             if ctx.c_real is None:
                 dw, acc = _grad_target(ctx.param, ctx.slot, wc)
-                _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device, acts=(dy, xc))
+                key = ("b200_conv2d_wgrad",) + tuple(g.value for g in geom)
+                _load_choices()
+                if _tc_mode == "auto" and key not in _choice and not torch.cuda.is_current_stream_capturing():
+                    # first sight of the shape: tune in line (the tuner synchronises), side streams from the next call
+                    _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device, acts=(dy, xc))
+                else:
+                    _run_on_side(dy.device, (dy, xc, dw), lambda: _conv_call(
+                        "b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw), _i(int(acc))), geom, dy.device, acts=(dy, xc)))
             else:
                 dw_pad = torch.empty_like(wc)
                 _conv_call("b200_conv2d_wgrad", (_ptr(dy), _ptr(xc), _ptr(dw_pad), _i(0)), geom, dy.device, acts=(dy, xc))

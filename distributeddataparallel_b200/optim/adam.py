@@ -21,6 +21,28 @@ class Adam(torch.optim.Adam):
         self._decoupled = decoupled
         self._tables = {}
 
+    def sync_hyper(self) -> None:
+        """Push changed hyper-parameters to the device-side table a captured step reads."""
+        for gi, group in enumerate(self.param_groups):
+            tab = self._tables.get(gi)
+            if tab is not None:
+                b1, b2 = group["betas"]
+                tab[1].set_hyper((group["lr"], b1, b2, group["eps"], group["weight_decay"], float(self._decoupled),
+                                  float(group["maximize"]), 1.0))
+
+    def load_state_dict(self, state_dict):
+        """Stock loader, then moments back to fp32 (the stock loader casts state to the parameter dtype; the fused
+        kernel keeps fp32 moments for bf16 parameters)."""
+        super().load_state_dict(state_dict)
+        for st in self.state.values():
+            for k in ("exp_avg", "exp_avg_sq"):
+                v = st.get(k)
+                if torch.is_tensor(v) and v.is_cuda and v.dtype != torch.float32:
+                    st[k] = v.to(torch.float32)
+            if torch.is_tensor(st.get("step")) and st["step"].dtype != torch.float32:
+                st["step"] = st["step"].to(torch.float32)
+        self._tables.clear()
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -42,6 +64,7 @@ class Adam(torch.optim.Adam):
             if self._native and ps[0].is_cuda and ops.native_enabled():
                 from ..ops import native
 
+                native.join_side_streams(ps[0].device)
                 native.fused_adam(self._tables, gi, ps, [p.grad for p in ps],
                                   [self.state[p]["exp_avg"] for p in ps],
                                   [self.state[p]["exp_avg_sq"] for p in ps],

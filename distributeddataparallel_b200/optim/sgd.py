@@ -39,22 +39,50 @@ class SGD(torch.optim.SGD):
                 continue
             from ..ops import native
 
+            native.join_side_streams(ps[0].device)       # weight gradients may still be in flight on a side stream
             mom = group["momentum"]
             bufs = None
             first = False
             if mom != 0:
-                bufs = []
-                for p in ps:
-                    st = self.state[p]
-                    if st.get("momentum_buffer") is None:
-                        # torch initialises the buffer with the first gradient (no dampening)
-                        st["momentum_buffer"] = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.preserve_format)
-                        first = True
-                    bufs.append(st["momentum_buffer"])
+                fresh = [p for p in ps if self.state[p].get("momentum_buffer") is None]
+                # torch initialises a momentum buffer with the first gradient (no dampening).  The fused kernel
+                # does that for the whole group through one flag, so it is used only when EVERY buffer is new;
+                # a parameter that joins later gets its buffer initialised here, on its own.
+                first = len(fresh) == len(ps)
+                for p in fresh:
+                    if first:
+                        buf = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.preserve_format)
+                    else:
+                        g = -p.grad if group["maximize"] else p.grad
+                        if group["weight_decay"] != 0:
+                            g = g.add(p, alpha=group["weight_decay"])
+                        buf = g.detach().to(torch.float32).clone(memory_format=torch.preserve_format)
+                        buf.div_(mom)        # the kernel's buf = mom * buf + (1 - dampening) * g is then undone below
+                        buf.sub_(g.to(torch.float32), alpha=(1 - group["dampening"]) / mom)
+                    self.state[p]["momentum_buffer"] = buf
+                bufs = [self.state[p]["momentum_buffer"] for p in ps]
             native.fused_sgd(self._tables, gi, ps, [p.grad for p in ps], bufs, lr=group["lr"],
                              momentum=mom, dampening=group["dampening"], weight_decay=group["weight_decay"],
                              nesterov=group["nesterov"], maximize=group["maximize"], first_step=first)
         return loss
+
+    def sync_hyper(self) -> None:
+        """Push changed hyper-parameters (a scheduler moved ``lr``) to the device-side table a captured step reads."""
+        for gi, group in enumerate(self.param_groups):
+            tab = self._tables.get(gi)
+            if tab is not None:
+                tab[1].set_hyper((group["lr"], group["momentum"], group["dampening"], group["weight_decay"],
+                                  float(group["nesterov"]), float(group["maximize"]), 0.0, 1.0))
+
+    def load_state_dict(self, state_dict):
+        """Stock loader, then momentum buffers back to fp32: ``torch.optim.Optimizer.load_state_dict`` casts
+        floating-point state to the parameter's dtype, and the fused kernels keep fp32 state for bf16 params."""
+        super().load_state_dict(state_dict)
+        for st in self.state.values():
+            buf = st.get("momentum_buffer")
+            if torch.is_tensor(buf) and buf.is_cuda and buf.dtype != torch.float32:
+                st["momentum_buffer"] = buf.to(torch.float32)
+        self._tables.clear()
 
     @staticmethod
     def _plain(group, p, g, state):

@@ -87,6 +87,10 @@ class C10dComm(CommBase):
 
     def launch(self, index: int, flat: torch.Tensor, is_last: bool):
         self.launches += 1
+        if flat.is_cuda:
+            from ..ops import native
+
+            native.join_side_streams(flat.device)      # weight gradients written on the side streams
         if self.world_size == 1:
             return _Done()
         flat.div_(self.divisor)
@@ -101,6 +105,10 @@ class NoComm(CommBase):
 
     def launch(self, index, flat, is_last):
         self.launches += 1
+        if flat.is_cuda:
+            from ..ops import native
+
+            native.join_side_streams(flat.device)
         return _Done()
 
     def broadcast_(self, flat, src=0):
@@ -159,6 +167,17 @@ class HookComm(CommBase):
 
     def launch(self, index: int, flat: torch.Tensor, is_last: bool):
         self.launches += 1
+        # the built-in hooks have fused forms on the P2P data plane: plain average, or fp32 buckets with a 16-bit wire
+        # format accumulated in fp32 (one kernel over NVLink instead of cast + NCCL all-reduce + cast back)
+        fused = getattr(self.hook, "_b200_fused", None)
+        if fused is not None and self.inner.name == "p2p" and self.inner.world_size > 1 and \
+                (self.state is None or self.state is self.group or self.state is dist.group.WORLD):
+            self.fused_launches = getattr(self, "fused_launches", 0) + 1
+            return self.inner.launch(index, flat, is_last, wire=None if fused == "allreduce" else fused)
+        if flat.is_cuda:
+            from ..ops import native
+
+            native.join_side_streams(flat.device)      # weight gradients written on the side streams
         grads, params = self._bucket_info(index)
         bucket = GradBucket(index, flat, grads, params, is_last)
         fut = self.hook(self.state, bucket)
@@ -208,6 +227,10 @@ def _compress_hook(dtype: torch.dtype):
 
 fp16_compress_hook = _compress_hook(torch.float16)   # default_hooks.py:87-134 equivalent
 bf16_compress_hook = _compress_hook(torch.bfloat16)
+# markers read by HookComm: on the P2P data plane these hooks are served by fused kernels (csrc/kernels/comm.cu)
+allreduce_hook._b200_fused = "allreduce"
+fp16_compress_hook._b200_fused = torch.float16
+bf16_compress_hook._b200_fused = torch.bfloat16
 
 
 # ---------------------------------------------------------------------------------------

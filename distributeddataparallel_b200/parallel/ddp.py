@@ -103,6 +103,7 @@ class DistributedDataParallel(nn.Module):
         self._join_throw = False
         self._rebuilt_bucket_sizes: List[int] = []
         self._graph_mode = False
+        self._buffers_ahead = False        # rank 0's buffers for the next forward were already broadcast
 
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
@@ -127,6 +128,13 @@ class DistributedDataParallel(nn.Module):
             self.first_bucket_bytes, self.bucket_bytes_cap)
         self._initial_bucket_sizes = list(self.reducer.bucket_sizes())
         self._publish_grad_slots()
+        if self._comm.name == "p2p" and self.world_size > 1:
+            # stream the last bucket (the one whose final gradient is the stem's weight gradient): pieces are
+            # reduced as they become ready, the last few KB go through the single-exchange push kernel
+            import os
+
+            spec = os.environ.get("B200DDP_TAIL_SPLITS", f"{1 << 20},{64 << 10}")
+            self.reducer.set_tail_splits([int(v) for v in spec.split(",") if v.strip()])
 
     # -- construction helpers --------------------------------------------------------------
     @staticmethod
@@ -169,19 +177,20 @@ class DistributedDataParallel(nn.Module):
 
             grad_bytes = sum(p.numel() * p.element_size() for p in self._params)
             buf_bytes = sum(b.numel() * b.element_size() + 16 for b in self.module.buffers())
+            from .p2p import ArenaUnavailable
+
             p2p, ok = None, 1
             try:
                 p2p = P2PComm(self.process_group, self.device, algo=self.allreduce_algo)
                 p2p.reserve(grad_bytes, buf_bytes)
-            except RuntimeError as e:
+            except ArenaUnavailable as e:
+                # raised by EVERY rank at the same point of the staged arena set-up (parallel/p2p.py), so all
+                # ranks fall back (or fail) together and no peer is left inside a collective
+                if p2p is not None:
+                    p2p.close()
                 if not auto:
                     raise
                 ok, self._p2p_error = 0, str(e)
-            if auto and self.world_size > 1:
-                # every rank must pick the same data plane
-                flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
-                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.process_group)
-                ok = int(flag.item())
             if ok:
                 return p2p
             import warnings
@@ -239,7 +248,37 @@ class DistributedDataParallel(nn.Module):
                 self._rebuild_buckets()
         if self.broadcast_buffers and self.world_size > 1 and self._buffers_for_sync \
                 and self.require_backward_grad_sync:
-            self._sync_buffers()
+            if self._buffers_ahead and self._buffer_src == 0:
+                self._buffers_ahead = False
+                self._comm.wait_buffers_ahead()      # already broadcast under the previous backward
+            else:
+                self._sync_buffers()
+
+    def _post_forward(self) -> None:
+        """Issue the NEXT forward's buffer broadcast now, on the communication stream: rank 0's running statistics
+        are final as soon as its forward is done, so K3 overlaps the backward pass instead of heading the next step
+        (same values as the stock pre-forward broadcast, /root/reference/dpp.py:50 -> distributed.py _pre_forward)."""
+        ahead = getattr(self._comm, "sync_buffers_ahead", None)
+        if (ahead is None or self._join_enabled or self._buffer_src != 0 or not self.training
+                or not torch.is_grad_enabled() or not self.will_sync_module_buffers()):
+            return
+        with torch.no_grad():
+            self._collectives["broadcast"] += ahead(self.module, self._buffers_for_sync)
+        self._buffers_ahead = True
+
+    def load_state_dict(self, *args, **kwargs):
+        self._buffers_ahead = False          # buffers changed behind the broadcast: the next forward syncs in line
+        return super().load_state_dict(*args, **kwargs)
+
+    def check_health(self, sync: bool = False) -> None:
+        """Raise if a collective kernel on this rank gave up waiting for a peer (dead or stalled rank).  Reads one
+        word of pinned host memory: cheap enough to call after every step (``sync=True`` first drains the GPU)."""
+        comm = self._comm
+        while comm is not None:
+            check = getattr(comm, "check", None)
+            if check is not None:
+                check(sync=sync)
+            comm = getattr(comm, "inner", None)
 
     def _rebuild_buckets(self) -> None:
         order = torch.tensor(self.reducer.rebuild_order(), dtype=torch.int64)
@@ -251,6 +290,13 @@ class DistributedDataParallel(nn.Module):
             dist.broadcast(order, src=0, group=self.process_group)     # ... and rank 0's order
             self._collectives["broadcast"] += 2
         self.reducer.rebuild_buckets(order.cpu().tolist())
+        if self.device.type == "cuda" and self.world_size > 1:
+            # iteration 0 has shown every convolution shape to the tuner: agree on ONE table of kernel variants so
+            # that all ranks run the same code from here on (and persist it for the next run)
+            from ..ops import native
+
+            native.sync_choices(self.process_group)
+            native.save_choices()
         self._rebuilt_bucket_sizes = list(self.reducer.bucket_sizes())
         self._publish_grad_slots()
 
@@ -267,6 +313,10 @@ class DistributedDataParallel(nn.Module):
         with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
             self._pre_forward()
             out = self.module(*inputs, **kwargs)
+            self._post_forward()
+            if torch.is_grad_enabled():
+                for p in self._params:
+                    p._slot_claimed = False      # one in-place writer per parameter per backward (ops/native.py)
             if torch.is_grad_enabled() and self.require_backward_grad_sync:
                 outs = [t for t in _flatten(out) if isinstance(t, torch.Tensor)] if self.find_unused_parameters else []
                 self.reducer.prepare_for_backward(outs)
@@ -391,6 +441,7 @@ class DistributedDataParallel(nn.Module):
             rank=self.rank,
             initial_bucket_sizes=self._initial_bucket_sizes,
             rebuilt_bucket_sizes=self._rebuilt_bucket_sizes,
+            launch_unit_sizes=list(self.reducer.launch_unit_sizes()),
             collectives=dict(self._collectives),
             bucket_launches=self._comm.launches,
         )

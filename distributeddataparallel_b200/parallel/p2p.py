@@ -43,10 +43,10 @@ def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
 
 
 def _pack_ctx(bufs: Sequence[int], flags: Sequence[int], epochs: int, error: int, rank: int, world: int,
-              channel: int, emulate: int, multicast: int = 0) -> ctypes.Array:
+              channel: int, emulate: int, multicast: int = 0, timeout_ns: int = 0) -> ctypes.Array:
     b = list(bufs) + [0] * (8 - len(bufs))
     f = list(flags) + [0] * (8 - len(flags))
-    raw = struct.pack("<8Q8QQQ4iQ", *b, *f, epochs, error, rank, world, channel, emulate, multicast)
+    raw = struct.pack("<8Q8QQQ4iQQ", *b, *f, epochs, error, rank, world, channel, emulate, multicast, timeout_ns)
     lib = native.load_library()
     assert len(raw) == lib.b200_comm_ctx_bytes(), (len(raw), lib.b200_comm_ctx_bytes())
     return ctypes.create_string_buffer(raw, len(raw))
@@ -54,15 +54,47 @@ def _pack_ctx(bufs: Sequence[int], flags: Sequence[int], epochs: int, error: int
 
 def _lib():
     lib = native.load_library()
-    for name in ("b200_comm_signal_bytes", "b200_comm_epoch_bytes", "b200_allreduce_oneshot_max_bytes"):
+    for name in ("b200_comm_signal_bytes", "b200_comm_epoch_bytes", "b200_allreduce_oneshot_max_bytes",
+                 "b200_allreduce_push_max_bytes", "b200_allreduce_push_stage_bytes"):
         getattr(lib, name).restype = ctypes.c_size_t
     return lib
 
 
-class SymmetricArena:
-    """One IPC-shared device block per rank with a bump allocator (same sequence on all ranks)."""
+def comm_timeout_ns() -> int:
+    """Bound on every in-kernel wait for a peer (``B200DDP_COMM_TIMEOUT_S``, default 600 s: the NCCL
+    process-group timeout the reference inherits through /root/reference/dpp.py:21)."""
+    return int(float(os.environ.get("B200DDP_COMM_TIMEOUT_S", "600")) * 1e9)
 
-    def __init__(self, group, device: torch.device, nbytes: int, provider: str = "ipc") -> None:
+
+class ArenaUnavailable(RuntimeError):
+    """Raised by EVERY rank together when the symmetric arena cannot be set up on some rank."""
+
+
+def _agree(group, local_error: str) -> Optional[str]:
+    """Collective: every rank contributes "" or an error; returns None when all succeeded, else one message
+    (the same on every rank), so that all ranks take the same branch."""
+    world = dist.get_world_size(group)
+    gathered: List[Optional[str]] = [None] * world
+    dist.all_gather_object(gathered, local_error or "", group=group)
+    bad = [(r, e) for r, e in enumerate(gathered) if e]
+    return None if not bad else f"rank {bad[0][0]}: {bad[0][1]}"
+
+
+class SymmetricArena:
+    """One device block per rank, mapped into every peer, with a bump allocator (same sequence on all ranks).
+
+    Providers (``B200DDP_ARENA``):
+
+    * ``vmm`` (default): this framework's own allocator in C++ (``csrc/runtime/vmm_arena.cpp``) -- ``cuMemCreate`` +
+      POSIX-fd export over a unix socket + ``cuMemMap`` of every peer, plus an NVLink *multicast* object all ranks
+      bind to (``cuMulticastCreate/AddDevice/BindMem``) where the device supports it, which enables the NVLS kernels;
+    * ``ipc``: ``cudaMalloc`` + CUDA IPC handles (no multicast); the fallback when the VMM path is unavailable.
+
+    Set-up is staged; after every stage the ranks agree on the outcome, so a failure on one rank makes ALL ranks
+    raise :class:`ArenaUnavailable` at the same point instead of leaving peers inside a collective.
+    """
+
+    def __init__(self, group, device: torch.device, nbytes: int, provider: str = "vmm") -> None:
         lib = _lib()
         self.group, self.device = group, device
         self.world = dist.get_world_size(group)
@@ -70,41 +102,85 @@ class SymmetricArena:
         self.nbytes = int(-(-nbytes // (2 << 20)) * (2 << 20))
         self.multicast = 0
         self.provider = provider
+        self._vmm = None
+        self._opened: List[int] = []
+        self._ipc_base = 0
         assert lib.b200_comm_signal_bytes() + lib.b200_comm_epoch_bytes() + 256 <= HEADER_BYTES
         torch.cuda.set_device(device)
-        if provider == "symm_mem":
-            # PyTorch's symmetric-memory allocator (CUDA VMM + NVLink multicast object) as the memory
-            # provider: same peer-pointer model, plus a multicast address for the NVLS kernels.  Only
-            # allocation / handle exchange is delegated (control plane); all kernels are ours.
-            import torch.distributed._symmetric_memory as symm_mem
+        torch.zeros(1, device=device)                 # make sure the primary context exists and is current
+        if provider == "vmm":
+            err = self._init_vmm()
+            if err is not None:
+                if os.environ.get("B200DDP_ARENA") == "vmm":
+                    raise ArenaUnavailable(f"VMM arena unavailable ({err})")
+                self.provider = provider = "ipc"
+                self.vmm_error = err
+        if provider == "ipc":
+            err = self._init_ipc(lib)
+            if err is not None:
+                raise ArenaUnavailable(f"CUDA IPC arena unavailable ({err})")
+        elif provider != "vmm":
+            raise ValueError(f"unknown arena provider {provider!r}")
+        self.memory = _as_tensor(self.base, self.nbytes, device)      # uint8 view of the local arena
+        self.memory.zero_()
+        torch.cuda.synchronize(device)
+        self._finish_init(lib)
 
-            pg = group if group is not None else dist.group.WORLD
-            symm_mem.enable_symm_mem_for_group(pg.group_name)
-            self._symm_tensor = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
-            hdl = symm_mem.rendezvous(self._symm_tensor, pg.group_name)
-            self._symm_handle = hdl
-            self.base = int(self._symm_tensor.data_ptr())
-            self.peer_base = [int(p) for p in hdl.buffer_ptrs]
-            self.multicast = int(hdl.multicast_ptr or 0)       # 0 when the box exposes no NVLink multicast
-            self._opened = []
-            self.memory = self._symm_tensor
-            self.memory.zero_()
-            self._finish_init(lib)
-            return
+    # -- providers ---------------------------------------------------------------------------
+    def _init_vmm(self) -> Optional[str]:
+        from .. import _C
+
+        tokens: List[Optional[str]] = [None] * self.world
+        dist.all_gather_object(tokens, os.urandom(6).hex(), group=self.group)
+        session = f"{os.environ.get('MASTER_PORT', '0')}-{tokens[0]}"       # rank 0's token names the socket namespace
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        vmm = _C.VmmArena(idx, self.nbytes, self.rank, self.world, session)
+        stages = (("alloc", vmm.alloc_local), ("fd exchange", vmm.exchange), ("map peers", vmm.map_peers))
+        for name, fn in stages:
+            try:
+                local = fn()
+            except Exception as e:  # pragma: no cover
+                local = repr(e)
+            err = _agree(self.group, f"{name}: {local}" if local else "")
+            if err is not None:
+                vmm.close()
+                return err
+        self._vmm = vmm
+        self.nbytes = int(vmm.nbytes())
+        self.base = int(vmm.base())
+        self.peer_base = [int(vmm.peer_base(r)) for r in range(self.world)]
+        # NVLink multicast (NVLS): optional -- every rank must succeed at every stage or nobody uses it
+        if os.environ.get("B200DDP_MULTICAST", "1") != "0":
+            err = _agree(self.group, vmm.multicast_create())
+            if err is None:
+                err = _agree(self.group, vmm.multicast_bind())
+                if err is None:
+                    self.multicast = int(vmm.multicast_base())
+            self.multicast_error = err
+        return None
+
+    def _init_ipc(self, lib) -> Optional[str]:
         ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        local = ""
         rc = lib.b200_arena_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(ptr))
         if rc != 0:
-            raise RuntimeError(f"arena cudaMalloc({self.nbytes}) failed: CUDA error {rc}")
-        self.base = int(ptr.value)
-        handle = (ctypes.c_ubyte * 64)()
-        rc = lib.b200_ipc_get_handle(ctypes.c_void_p(self.base), handle)
-        if rc != 0:
-            raise RuntimeError(f"cudaIpcGetMemHandle failed: CUDA error {rc}")
-        gathered: List[Optional[bytes]] = [None] * self.world
-        dist.all_gather_object(gathered, bytes(handle), group=group)
-        self.peer_base: List[int] = []
-        self._opened: List[int] = []
-        for r, h in enumerate(gathered):
+            local = f"cudaMalloc({self.nbytes}) failed: CUDA error {rc}"
+        else:
+            self._ipc_base = int(ptr.value)
+            rc = lib.b200_ipc_get_handle(ctypes.c_void_p(self._ipc_base), handle)
+            if rc != 0:
+                local = f"cudaIpcGetMemHandle failed: CUDA error {rc}"
+        gathered: List[Optional[tuple]] = [None] * self.world
+        dist.all_gather_object(gathered, (local, bytes(handle)), group=self.group)
+        bad = [(r, e) for r, (e, _) in enumerate(gathered) if e]
+        if bad:
+            self._free_ipc(lib)
+            return f"rank {bad[0][0]}: {bad[0][1]}"
+        self.base = self._ipc_base
+        self.peer_base = []
+        local = ""
+        for r, (_, h) in enumerate(gathered):
             if r == self.rank:
                 self.peer_base.append(self.base)
                 continue
@@ -112,19 +188,35 @@ class SymmetricArena:
             buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
             rc = lib.b200_ipc_open_handle(buf, ctypes.byref(out))
             if rc != 0:
-                raise RuntimeError(f"cudaIpcOpenMemHandle(rank {r}) failed: CUDA error {rc}; "
-                                   "peer access over NVLink is required for comm='p2p'")
+                local = local or (f"cudaIpcOpenMemHandle(rank {r}) failed: CUDA error {rc}; peer access over "
+                                  "NVLink is required for comm='p2p'")
+                self.peer_base.append(0)
+                continue
             self.peer_base.append(int(out.value))
             self._opened.append(int(out.value))
-        self.memory = _as_tensor(self.base, self.nbytes, device)      # uint8 view of the local arena
-        self._finish_init(lib)
+        err = _agree(self.group, local)
+        if err is not None:
+            self._free_ipc(lib)
+        return err
+
+    def _free_ipc(self, lib) -> None:
+        for p in self._opened:
+            lib.b200_ipc_close_handle(ctypes.c_void_p(p))
+        self._opened = []
+        if self._ipc_base:
+            lib.b200_arena_free(ctypes.c_void_p(self._ipc_base))
+            self._ipc_base = 0
 
     def _finish_init(self, lib) -> None:
         group = self.group
         self._cursor = HEADER_BYTES
         sig = lib.b200_comm_signal_bytes()
         self.epochs_ptr = self.base + sig
-        self.error_ptr = self.base + sig + lib.b200_comm_epoch_bytes()
+        # the error word lives in pinned host memory: kernels store to it over PCIe only when a wait times out,
+        # the host reads it with a plain load -- cheap enough to poll after every step
+        self._error_host = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self.error_ptr = self._error_host.data_ptr()
+        self.timeout_ns = comm_timeout_ns()
         self._ctx: Dict[int, ctypes.Array] = {}
         dist.barrier(group=group)      # everyone has mapped everyone before the first kernel
 
@@ -132,8 +224,12 @@ class SymmetricArena:
         c = self._ctx.get(channel)
         if c is None:
             c = self._ctx[channel] = _pack_ctx(self.peer_base, self.peer_base, self.epochs_ptr, self.error_ptr,
-                                               self.rank, self.world, channel, 0, self.multicast)
+                                               self.rank, self.world, channel, 0, self.multicast, self.timeout_ns)
         return c
+
+    def set_timeout(self, seconds: float) -> None:
+        self.timeout_ns = int(seconds * 1e9)
+        self._ctx.clear()
 
     def alloc(self, nbytes: int, align: int = 256) -> int:
         off = -(-self._cursor // align) * align
@@ -153,14 +249,29 @@ class SymmetricArena:
         return off if 0 <= off and off + t.numel() * t.element_size() <= self.nbytes else None
 
     def error_word(self) -> int:
-        off = self.error_ptr - self.base
-        return int(self.memory[off:off + 4].view(torch.int32).item()) & 0xFFFFFFFF
+        """Host-side read of the error word (no CUDA call, no synchronisation)."""
+        return int(self._error_host[0]) & 0xFFFFFFFF
+
+    def seed_epochs(self, value: int) -> None:
+        """Test hook: start every epoch counter (and every flag, on every rank -- call it on all ranks, then
+        barrier) at ``value``, e.g. 2**32 - 8 to exercise the wraparound."""
+        lib = _lib()
+        sig, ep = lib.b200_comm_signal_bytes(), lib.b200_comm_epoch_bytes()
+        v = value & 0xFFFFFFFF
+        v = v - (1 << 32) if v >= (1 << 31) else v
+        self.memory[:sig + ep].view(torch.int32).fill_(v)
+        torch.cuda.synchronize(self.device)
 
     def close(self) -> None:
         lib = native.load_library()
-        for p in self._opened:
-            lib.b200_ipc_close_handle(ctypes.c_void_p(p))
-        self._opened = []
+        if self._vmm is not None:
+            torch.cuda.synchronize(self.device)
+            self._vmm.close()
+            self._vmm = None
+        else:
+            for p in self._opened:
+                lib.b200_ipc_close_handle(ctypes.c_void_p(p))
+            self._opened = []
 
 
 class _EventHandle:
@@ -190,8 +301,11 @@ class P2PComm(CommBase):
         self.stream = torch.cuda.Stream(device=device, priority=-1)
         self._staging: Optional[int] = None
         self._staging_bytes = 0
+        self._push_stage: Dict[int, int] = {}      # channel -> arena offset of the push all-reduce staging object
         self._buffer_region = None
+        self._ahead_event: Optional[torch.cuda.Event] = None
         self.bytes_reduced = 0
+        self.algo_counts: Dict[str, int] = {}
         # observability / safety switches
         self.timing = os.environ.get("B200DDP_COMM_TIMING", "0") != "0"     # device-time every bucket reduction
         self.debug_check = os.environ.get("B200DDP_DEBUG_COMM", "0") != "0"  # cross-check each bucket against NCCL
@@ -207,9 +321,13 @@ class P2PComm(CommBase):
         env = os.environ.get("B200DDP_ARENA_MB")
         if self._arena_bytes is None:
             staging = min(max(grad_bytes, 16 << 20), 256 << 20)
-            self._arena_bytes = (int(env) << 20) if env else int(2.3 * grad_bytes) + buffer_bytes + staging + (8 << 20)
-        provider = os.environ.get("B200DDP_ARENA", "symm_mem" if self.algo == "nvls" else "ipc")
+            self._arena_bytes = (int(env) << 20) if env else int(2.3 * grad_bytes) + buffer_bytes + staging + (20 << 20)
+        provider = os.environ.get("B200DDP_ARENA", "vmm")
         self.arena = SymmetricArena(self.group, self.device, self._arena_bytes, provider=provider)
+        lib = _lib()
+        self.push_max = int(lib.b200_allreduce_push_max_bytes())
+        for ch in (self.GRAD_CHANNEL, self.MAIN_CHANNEL):
+            self._push_stage[ch] = self.arena.alloc(int(lib.b200_allreduce_push_stage_bytes()))
         if self.algo == "nvls" and not self.arena.multicast:
             import warnings
 
@@ -229,32 +347,48 @@ class P2PComm(CommBase):
         return t
 
     # -- collectives ------------------------------------------------------------------------
+    ALGO_NAMES = {1: "oneshot", 2: "twoshot", 3: "nvls", 4: "push"}
+
     def _pick_algo(self, nbytes: int) -> int:
+        """1 one-shot, 2 two-shot, 3 NVLS (multimem), 4 push (single flag exchange).  ``auto``: push up to 256 KB
+        (latency: one exchange instead of two barriers), NVLS above that wherever the arena is multicast-bound (the
+        switch reduces: measured faster than two-shot from 1 MB up on 8 GPUs), else two-shot."""
         lib = _lib()
         if self.algo == "oneshot" and nbytes <= lib.b200_allreduce_oneshot_max_bytes():
             return 1
+        if self.algo == "push" and nbytes <= self.push_max:
+            return 4
         if self.algo == "nvls":
             return 3 if (self.arena is not None and self.arena.multicast) else 2
         if self.algo == "twoshot":
             return 2
-        if self.algo == "auto" and nbytes <= self.oneshot_max:
-            return 1
-        # with a multicast-capable arena (B200DDP_ARENA=symm_mem) the in-switch reduction wins from ~256 KB up
-        # (8 GPUs, graph-timed: 44.7 MB 130 us vs 150 us two-shot; 256 MB 576 us vs 741 us)
-        if self.algo == "auto" and self.arena is not None and self.arena.multicast and nbytes >= (256 << 10):
-            return 3
+        if self.algo == "auto":
+            if nbytes <= min(self.oneshot_max, self.push_max):
+                return 4
+            if self.arena is not None and self.arena.multicast and nbytes >= (256 << 10):
+                return 3
         return 2
 
     def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype,
-                      blocks: Optional[int] = None) -> None:
+                      blocks: Optional[int] = None, algo: Optional[int] = None) -> int:
+        algo = self._pick_algo(nbytes) if algo is None else algo
+        if algo == 4:
+            native._call("b200_allreduce_push", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
+                         ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
+                         ctypes.c_size_t(self._push_stage[channel]), ctypes.c_void_p(stream.cuda_stream))
+            return algo
         native._call("b200_allreduce", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
                      ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
-                     ctypes.c_int(self._pick_algo(nbytes)), ctypes.c_int(blocks or self.max_blocks),
+                     ctypes.c_int(algo), ctypes.c_int(blocks or self.max_blocks),
                      ctypes.c_void_p(stream.cuda_stream))
+        return algo
 
-    def launch(self, index: int, flat: torch.Tensor, is_last: bool):
+    def launch(self, index: int, flat: torch.Tensor, is_last: bool, wire: Optional[torch.dtype] = None):
+        """Reduce one launch unit on the communication stream.  ``wire`` = bf16 / fp16: fp32 data travels in that
+        16-bit format and is accumulated in fp32 (the fused form of the compress comm hooks)."""
         self.launches += 1
         if self.world_size == 1:
+            native.join_side_streams(self.device)
             return _Done()
         off = self.arena.offset_of(flat) if self.arena is not None else None
         if off is None or flat.dtype not in _DTYPE_CODE:
@@ -265,7 +399,7 @@ class P2PComm(CommBase):
         if self.nvtx:
             torch.cuda.nvtx.range_push(f"b200ddp.bucket{index}.allreduce[{nbytes}B]")
         expect = None
-        if self.debug_check and not capturing:
+        if self.debug_check and not capturing and wire is None:
             expect = flat.detach().float().clone()
             dist.all_reduce(expect, group=self.group)
             expect /= self.divisor
@@ -278,8 +412,16 @@ class P2PComm(CommBase):
             t0.record(self.stream)
         # the last bucket of a backward pass has nothing left to overlap with: it may use more of the chip
         # (every rank takes the same decision, so the block counts agree)
-        self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype,
-                           blocks=self.last_blocks if is_last else None)
+        for ev in native.side_stream_events():        # weight gradients produced on the side streams (ops/native.py)
+            self.stream.wait_event(ev)
+        if wire is not None and flat.dtype == torch.float32 and nbytes % 32 == 0 and nbytes > self.push_max:
+            self.allreduce_wire16_(flat, wire, stream=self.stream, channel=self.GRAD_CHANNEL)
+            name = "wire16"
+        else:
+            algo = self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype,
+                                      blocks=self.last_blocks if is_last else None)
+            name = self.ALGO_NAMES[algo]
+        self.algo_counts[name] = self.algo_counts.get(name, 0) + 1
         done = torch.cuda.Event(enable_timing=t0 is not None)
         done.record(self.stream)
         if t0 is not None:
@@ -298,7 +440,9 @@ class P2PComm(CommBase):
     def stats(self) -> dict:
         """Device-timed per-bucket statistics (needs B200DDP_COMM_TIMING=1; eager steps only)."""
         out = {"bucket_launches": self.launches, "bytes_reduced": self.bytes_reduced,
-               "debug_max_rel_err_vs_nccl": self.debug_max_err}
+               "debug_max_rel_err_vs_nccl": self.debug_max_err, "algo_counts": dict(self.algo_counts),
+               "arena_provider": self.arena.provider if self.arena is not None else None,
+               "multicast": bool(self.arena is not None and self.arena.multicast)}
         done = [(a.elapsed_time(b), n) for a, b, n in self._timed if b.query()]
         if done:
             ms = sum(t for t, _ in done)
@@ -344,7 +488,7 @@ class P2PComm(CommBase):
         us = float(t.item()) * 1e3
         f = 2 * (self.world_size - 1) / self.world_size
         return {"bytes": nbytes, "us": round(us, 2), "bus_gbs": round(nbytes * f / (us * 1e-6) / 1e9, 1),
-                "algo": {1: "oneshot", 2: "twoshot", 3: "nvls"}[algo]}
+                "algo": self.ALGO_NAMES[algo]}
 
     def all_reduce_avg_(self, flat: torch.Tensor) -> None:
         """In-place average on the current stream (tensor inside the arena, or staged through it)."""
@@ -408,9 +552,7 @@ class P2PComm(CommBase):
                          ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream))
 
     # -- per-forward module-buffer sync (K3): one launch for every buffer of every dtype --------
-    def sync_buffers(self, module: torch.nn.Module, buffers: Sequence[torch.Tensor]) -> int:
-        if self.world_size == 1 or not buffers:
-            return 0
+    def _buffers_into_arena(self, buffers: Sequence[torch.Tensor]) -> None:
         if self._buffer_region is None:
             arena = self._need_arena()
             total = sum(-(-b.numel() * b.element_size() // 16) * 16 for b in buffers)
@@ -423,24 +565,88 @@ class P2PComm(CommBase):
                     b.data = view                      # the module's buffer now lives in the arena
                     off += -(-b.numel() * b.element_size() // 16) * 16
             self._buffer_region = (base, total)
+
+    def sync_buffers(self, module: torch.nn.Module, buffers: Sequence[torch.Tensor]) -> int:
+        if self.world_size == 1 or not buffers:
+            return 0
+        self._buffers_into_arena(buffers)
         base, total = self._buffer_region
         self._broadcast_on(torch.cuda.current_stream(self.device), base, total, 0)
         return 1
 
-    def check(self) -> None:
-        """Raise if a kernel gave up waiting for a peer (bounded spin)."""
+    def sync_buffers_ahead(self, module: torch.nn.Module, buffers: Sequence[torch.Tensor]) -> int:
+        """K3 for the NEXT forward, issued on the communication stream right after this forward: rank 0's
+        buffers are final once its forward has run, so the broadcast rides under the backward pass instead of
+        heading the next step.  ``wait_buffers_ahead`` orders the next forward after it."""
+        if self.world_size == 1 or not buffers:
+            return 0
+        self._buffers_into_arena(buffers)
+        base, total = self._buffer_region
+        cur = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        self.stream.wait_event(ready)
+        native._call("b200_broadcast", self.arena.ctx(self.GRAD_CHANNEL), ctypes.c_size_t(base),
+                     ctypes.c_size_t(total), ctypes.c_int(0), ctypes.c_int(self.max_blocks),
+                     ctypes.c_void_p(self.stream.cuda_stream))
+        self._ahead_event = torch.cuda.Event()
+        self._ahead_event.record(self.stream)
+        return 1
+
+    def wait_buffers_ahead(self) -> None:
+        ev, self._ahead_event = self._ahead_event, None
+        if ev is not None and not torch.cuda.is_current_stream_capturing():
+            torch.cuda.current_stream(self.device).wait_event(ev)
+
+    def join_stream(self) -> None:
+        """Order the current stream after everything issued on the communication stream (used before a capture
+        ends and by the optimizer when no gradient bucket handle carries the dependency)."""
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        torch.cuda.current_stream(self.device).wait_event(ev)
+
+    # -- compressed wire format (comm hooks) -----------------------------------------------------------------
+    def allreduce_wire16_(self, flat: torch.Tensor, wire: torch.dtype, stream: Optional[torch.cuda.Stream] = None,
+                          channel: Optional[int] = None) -> None:
+        """In-place average of an fp32 arena tensor with bf16 / fp16 on the wire and fp32 accumulation."""
+        off = self.arena.offset_of(flat)
+        nbytes = flat.numel() * flat.element_size()
+        if off is None or flat.dtype != torch.float32 or nbytes % 32 != 0:
+            raise RuntimeError("wire16 all-reduce needs an fp32 arena tensor whose size is a multiple of 32 bytes")
+        self._ensure_staging()
+        if nbytes // 2 > self._staging_bytes:
+            raise RuntimeError("bucket too large for the staging region")
+        stream = stream or torch.cuda.current_stream(self.device)
+        native._call("b200_allreduce_wire16", self.arena.ctx(self.MAIN_CHANNEL if channel is None else channel),
+                     ctypes.c_size_t(off), ctypes.c_size_t(nbytes), ctypes.c_int(1 if wire == torch.bfloat16 else 2),
+                     ctypes.c_float(1.0 / self.divisor), ctypes.c_size_t(self._staging),
+                     ctypes.c_int(self.max_blocks), ctypes.c_void_p(stream.cuda_stream))
+
+    # -- failure detection -------------------------------------------------------------------------------------
+    def check(self, sync: bool = True) -> None:
+        """Raise if a kernel gave up waiting for a peer (time-bounded waits).  The error word lives
+        in pinned host memory, so ``sync=False`` costs one host load and can run after every step."""
         if self.arena is not None:
-            torch.cuda.synchronize(self.device)
+            if sync:
+                torch.cuda.synchronize(self.device)
             w = self.arena.error_word()
             if w:
-                raise RuntimeError(f"P2P collective timed out waiting for rank {w & 0xFFFF} (error word {w:#x})")
+                raise RuntimeError(
+                    f"P2P collective timed out on rank {self.rank} waiting for rank {w & 0xFFFF} (error word {w:#x}, "
+                    f"limit {self.arena.timeout_ns / 1e9:.0f} s): the affected results were poisoned with NaN; a peer is "
+                    "dead or stalled -- aborting this rank")
+
+    def close(self) -> None:
+        if self.arena is not None:
+            self.arena.close()
+            self.arena = None
 
 
 class EmulatedWorld:
     """All ranks on ONE GPU: same kernels, one cooperative launch with blockIdx.y as the rank."""
 
     def __init__(self, world: int, device: torch.device | str = "cuda", arena_bytes: int = 64 << 20,
-                 max_blocks: int = 8) -> None:
+                 max_blocks: int = 8, timeout_s: float = 30.0) -> None:
         lib = _lib()
         self.world, self.device = world, torch.device(device)
         self.nbytes = arena_bytes
@@ -452,7 +658,8 @@ class EmulatedWorld:
                      for _ in range(world)]
         bases = [a.data_ptr() for a in self.arenas]
         pads = [p.data_ptr() for p in self.pads]
-        self._ctx = {ch: _pack_ctx(bases, pads, self.epochs.data_ptr(), self.error.data_ptr(), 0, world, ch, 1)
+        self._ctx = {ch: _pack_ctx(bases, pads, self.epochs.data_ptr(), self.error.data_ptr(), 0, world, ch, 1,
+                                   0, int(timeout_s * 1e9))
                      for ch in range(2)}
 
     def view(self, rank: int, offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
@@ -465,6 +672,26 @@ class EmulatedWorld:
                      ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.world if scale is None else scale),
                      ctypes.c_int(algo), ctypes.c_int(self.max_blocks),
                      ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def allreduce_push(self, offset: int, nbytes: int, dtype: torch.dtype, stage_off: int,
+                       scale: Optional[float] = None, channel: int = 0) -> None:
+        native._call("b200_allreduce_push", self._ctx[channel], ctypes.c_size_t(offset), ctypes.c_size_t(nbytes),
+                     ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.world if scale is None else scale),
+                     ctypes.c_size_t(stage_off), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def allreduce_wire16(self, offset: int, nbytes: int, wire: torch.dtype, stage_off: int,
+                         scale: Optional[float] = None, channel: int = 0) -> None:
+        native._call("b200_allreduce_wire16", self._ctx[channel], ctypes.c_size_t(offset), ctypes.c_size_t(nbytes),
+                     ctypes.c_int(1 if wire == torch.bfloat16 else 2),
+                     ctypes.c_float(1.0 / self.world if scale is None else scale), ctypes.c_size_t(stage_off),
+                     ctypes.c_int(self.max_blocks), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+
+    def seed_epochs(self, value: int) -> None:
+        v = value & 0xFFFFFFFF
+        v = v - (1 << 32) if v >= (1 << 31) else v
+        self.epochs.fill_(v)
+        for p in self.pads:
+            p.fill_(v)
 
     def broadcast(self, offset: int, nbytes: int, root: int, channel: int = 1) -> None:
         native._call("b200_broadcast", self._ctx[channel], ctypes.c_size_t(offset), ctypes.c_size_t(nbytes),

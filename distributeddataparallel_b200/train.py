@@ -88,7 +88,20 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
     device = torch.device("cuda", rank % torch.cuda.device_count()) if device_type == "cuda" else torch.device("cpu")
     ops.set_native(cfg.native_ops)
 
-    dataset = cifar10(cfg.data_root, train=True, synthetic=cfg.synthetic, n=cfg.dataset_size, rank=rank)   # :33
+    is_lm = cfg.model.lower().startswith("gpt2")
+    if cfg.dtype == "bf16" and not is_lm:
+        raise ValueError("--dtype bf16 applies to the transformer models (gpt2*); the convolutional models run fp32 "
+                         "storage with TF32 tensor-core math")
+    if is_lm:
+        dataset = SyntheticTokens(n=cfg.dataset_size, seq_len=cfg.seq_len, seed=1234)
+    elif cfg.image_size != 32:
+        from .data import SyntheticCIFAR10
+
+        if not cfg.synthetic:
+            raise ValueError("--image-size other than 32 needs --synthetic (CIFAR-10 images are 32x32)")
+        dataset = SyntheticCIFAR10(n=cfg.dataset_size, seed=1234, image_size=cfg.image_size)
+    else:
+        dataset = cifar10(cfg.data_root, train=True, synthetic=cfg.synthetic, n=cfg.dataset_size, rank=rank)   # :33
     sampler = DistributedSampler(dataset, num_replicas=world_size, rank=rank, shuffle=True)               # :34
     if hasattr(dataset, "data"):
         dataloader = DeviceLoader(dataset, cfg.batch_size, sampler, device)                               # :35
@@ -98,6 +111,8 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
         dataloader = DataLoader(dataset, batch_size=cfg.batch_size, sampler=sampler)
 
     model = build_model(cfg).to(device)                                     # dpp.py:38
+    if cfg.dtype == "bf16":
+        model = model.to(torch.bfloat16)
     model = DDP(model, device_ids=[device.index] if device.type == "cuda" else None,
                 broadcast_buffers=cfg.broadcast_buffers, bucket_cap_mb=cfg.bucket_cap_mb,
                 first_bucket_mb=cfg.first_bucket_mb, comm=cfg.comm, allreduce_algo=cfg.allreduce_algo)   # :39
@@ -123,6 +138,8 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
             loss = step_fn(data, target)                                    # dpp.py:49-53
             global_step += 1
             seen += data.shape[0]
+            if batch_idx % cfg.log_interval == 0:
+                model.check_health(sync=False)      # a collective that timed out on this rank raises here
             if batch_idx % cfg.log_interval == 0 and rank == 0:             # dpp.py:54-55
                 val = loss.item()
                 history.append(val)
@@ -135,6 +152,7 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
                 break
         if cfg.checkpoint_path and (done or epoch == epochs - 1 or
                                     (cfg.checkpoint_every and (epoch + 1) % cfg.checkpoint_every == 0)):
+            model.check_health(sync=True)           # never persist parameters updated from a failed reduction
             save_checkpoint(cfg.checkpoint_path, model, optimizer, epoch=epoch + 1, step=global_step, sampler=sampler)
         if done:
             break
@@ -143,5 +161,6 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
     if cfg.print_ddp_stats and rank == 0:
         print(format_ddp_stats(stats["ddp"], seen * world_size, time.time() - t0), flush=True)
     del step_fn
+    model.check_health(sync=True)
     cleanup()                                                               # dpp.py:57
     return stats

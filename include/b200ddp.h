@@ -191,7 +191,10 @@ int b200_xent_rows(const void* logits, const long long* target, void* dlogits, f
  * struct (csrc/kernels/comm.cu): arena and signal-pad base of every rank as mapped in this
  * process, local epoch counters, error word, rank/world/channel.  Objects are addressed by
  * byte offset inside the arena; all collectives are in place.
- * dtype 0 = fp32, 1 = bf16 (fp32 accumulate); algo 1 = one-shot, 2 = two-shot. */
+ * dtype 0 = fp32, 1 = bf16 (fp32 accumulate); algo 1 = one-shot, 2 = two-shot, 3 = NVLS (multimem through the
+ * arena's multicast mapping).  Every in-kernel wait is bounded by the context's timeout_ns (0 = 10 minutes): a
+ * collective whose peer does not arrive writes the context's error word, skips its peer traffic and NaN-fills its
+ * share of the local result. */
 int b200_comm_ctx_bytes(void);
 int b200_comm_max_blocks(void);
 size_t b200_comm_signal_bytes(void);
@@ -199,6 +202,16 @@ size_t b200_comm_epoch_bytes(void);
 size_t b200_allreduce_oneshot_max_bytes(void);
 int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, int algo,
                    int max_blocks, cudaStream_t stream);
+/* small messages (<= b200_allreduce_push_max_bytes()): one flag exchange instead of two barriers; `stage_off` is the
+ * arena offset of a per-channel staging object of b200_allreduce_push_stage_bytes() bytes */
+size_t b200_allreduce_push_max_bytes(void);
+size_t b200_allreduce_push_stage_bytes(void);
+int b200_allreduce_push(const void* ctx, size_t offset, size_t nbytes, int dtype, float scale, size_t stage_off,
+                        cudaStream_t stream);
+/* fp32 data with a 16-bit wire format (wire 1 = bf16, 2 = fp16) and fp32 accumulation: the fused form of the
+ * bf16/fp16 compress comm hooks.  nbytes % 32 == 0; staging object of nbytes/2 bytes at `stage_off`. */
+int b200_allreduce_wire16(const void* ctx, size_t offset, size_t nbytes, int wire, float scale, size_t stage_off,
+                          int max_blocks, cudaStream_t stream);
 int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks, cudaStream_t stream);
 int b200_barrier(const void* ctx, cudaStream_t stream);
 /* set-up helpers (these DO allocate / map memory; call once, outside any capture) */

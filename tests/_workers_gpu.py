@@ -31,9 +31,16 @@ def collectives_worker(rank, ws, port, out_dir):
     g = torch.Generator(device="cpu").manual_seed(rank)
     for dtype in (torch.float32, torch.bfloat16):
         for numel in (256, 65_536, 1 << 20, 5_000_000):
-            for algo in ("oneshot", "twoshot"):
+            for algo in ("oneshot", "twoshot", "push", "auto", "nvls"):
                 if algo == "oneshot" and numel * 4 > (4 << 20):
                     continue
+                if algo == "push" and numel * 4 > comm.push_max:
+                    continue
+                if algo == "nvls" and not comm.arena.multicast:
+                    continue
+                if numel == 65_536 and algo == "twoshot" and dtype == torch.float32:
+                    comm.arena.seed_epochs(2 ** 32 - 6)          # cross the 2^32 epoch boundary on real peers
+                    dist.barrier()
                 comm.algo = algo
                 flat = comm.allocate(numel, dtype, dev)
                 src = torch.randn(numel, generator=g).to(dtype).to(dev)
@@ -60,6 +67,10 @@ def collectives_worker(rank, ws, port, out_dir):
         rec["ok"] = False
         rec["fails"].append("broadcast")
     comm.check()
+    rec["provider"] = comm.arena.provider
+    rec["multicast"] = bool(comm.arena.multicast)
+    rec["multicast_error"] = getattr(comm.arena, "multicast_error", None)
+    rec["vmm_error"] = getattr(comm.arena, "vmm_error", None)
     torch.save(rec, os.path.join(out_dir, f"coll{rank}.pt"))
     d.cleanup()
 
@@ -79,16 +90,45 @@ def ddp_worker(rank, ws, port, out_dir):
         u = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).to(dev)
         return d.ops.preprocess_u8(u), torch.randint(0, 10, (32,), generator=g).to(dev)
 
-    # one eager step on both wrappers from identical state: averaged grads must agree with NCCL
+    # two eager steps (the second one runs on the rebuilt, tail-split bucket layout)
+    for _ in range(2):
+        x, y = batch()
+        opt.zero_grad()
+        d.CrossEntropyLoss()(model(x), y).backward()
+    # local gradients of one more batch, NOT reduced (no_sync): reduce exactly these with the product kernels through
+    # the real launch units, and with NCCL, and compare -- identical inputs, so the tolerance is rounding only
+    opt.zero_grad()
     x, y = batch()
-    d.CrossEntropyLoss()(model(x), y).backward()
-    d.CrossEntropyLoss()(ref_model(x), y).backward()
-    ga = torch.cat([p.grad.reshape(-1) for p in model.parameters()])
-    gb = torch.cat([p.grad.reshape(-1) for p in ref_model.parameters()])
-    rec = {"grad_err_vs_nccl": float((ga - gb).norm() / gb.norm())}
+    with model.no_sync():
+        d.CrossEntropyLoss()(model(x), y).backward()
+    torch.cuda.synchronize()
+    units = [model.reducer.bucket_flat(i) for i in range(model.reducer.num_buckets())]
+    expect = []
+    for flat in units:
+        e = flat.detach().clone()
+        dist.all_reduce(e)
+        expect.append(e / ws)
+    for i, flat in enumerate(units):
+        model.comm.launch(i, flat, i + 1 == len(units)).wait()
+    torch.cuda.synchronize()
+    rec = {"grad_err_vs_nccl": max(float((f - e).abs().max() / e.abs().max().clamp_min(1e-20))
+                                   for f, e in zip(units, expect)),
+           "launch_units": model._get_ddp_logging_data()["launch_unit_sizes"],
+           "algo_counts": dict(model.comm.algo_counts), "provider": model.comm.arena.provider,
+           "multicast": bool(model.comm.arena.multicast)}
+    del ref_model
     opt.zero_grad()
     for _ in range(8):
         step(*batch())
+    # the ragged tail: first sight eager, second sight captured as a second graph
+    def tail():
+        u = torch.randint(0, 256, (16, 32, 32, 3), dtype=torch.uint8, generator=g).to(dev)
+        return d.ops.preprocess_u8(u), torch.randint(0, 10, (16,), generator=g).to(dev)
+    step(*tail())
+    step(*batch())
+    step(*tail())
+    step(*batch())
+    rec["graphs"] = len(step._graphs)
     torch.cuda.synchronize()
     flat = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
     gathered = [torch.empty_like(flat) for _ in range(ws)]
@@ -144,8 +184,6 @@ def fused_wgrad_worker(rank, ws, port, out_dir):
                 rec["ok"] = False
                 rec["fails"].append((str(dtype), tok, n_out, k_in, same, err))
             # timing: fused vs unfused (GEMM into the arena slot, then the two-shot all-reduce)
-            def unfused():
-                native.gemm_tc(dy.t().contiguous() if False else dy, x, 2, out=None) if False else None
             e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             from distributeddataparallel_b200.ops import native_tf
             tmp = comm.allocate(n_out * k_in, torch.float32, dev).view(n_out, k_in) if dtype == torch.float32 else \
@@ -167,8 +205,83 @@ def fused_wgrad_worker(rank, ws, port, out_dir):
     d.cleanup()
 
 
+def hooks_worker(rank, ws, port, out_dir):
+    """Built-in comm hooks on the P2P data plane run as fused kernels (16-bit wire, fp32 accumulate)."""
+    d = _init(rank, ws, port)
+    from distributeddataparallel_b200.parallel import comm as hooks
+
+    dev = torch.device("cuda", rank)
+    rec = {}
+    for name, hook, tol in (("bf16", hooks.bf16_compress_hook, 3e-2), ("fp16", hooks.fp16_compress_hook, 5e-3),
+                            ("allreduce", hooks.allreduce_hook, 1e-5)):
+        torch.manual_seed(5)
+        model = d.DDP(d.SimpleCNN().to(dev), device_ids=[rank], comm="p2p")
+        model.register_comm_hook(None, hook)
+        g = torch.Generator(device="cpu").manual_seed(7 + rank)
+        x = d.ops.preprocess_u8(torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).to(dev))
+        y = torch.randint(0, 10, (32,), generator=g).to(dev)
+        with model.no_sync():
+            d.CrossEntropyLoss()(model(x), y).backward()
+        torch.cuda.synchronize()
+        units = [model.reducer.bucket_flat(i) for i in range(model.reducer.num_buckets())]
+        expect = []
+        for flat in units:
+            e = flat.detach().clone()
+            dist.all_reduce(e)
+            expect.append(e / ws)
+        for i, flat in enumerate(units):
+            model.comm.launch(i, flat, i + 1 == len(units)).wait()
+        torch.cuda.synchronize()
+        err = max(float((f - e).abs().max() / e.abs().max().clamp_min(1e-20)) for f, e in zip(units, expect))
+        same = True
+        for flat in units:
+            gathered = [torch.empty_like(flat) for _ in range(ws)]
+            dist.all_gather(gathered, flat)
+            same = same and all(torch.equal(gathered[0], t) for t in gathered)
+        rec[name] = {"err": err, "tol": tol, "same": same, "fused": getattr(model.comm, "fused_launches", 0),
+                     "algos": dict(model.comm.inner.algo_counts)}
+        model.check_health(sync=True)
+        del model
+    torch.save(rec, os.path.join(out_dir, f"hooks{rank}.pt"))
+    d.cleanup()
+
+
+def dead_rank_worker(rank, ws, port, out_dir):
+    """The last rank dies mid-training; the survivors must raise within a bounded time (no hung GPU)."""
+    import time
+
+    os.environ["B200DDP_COMM_TIMEOUT_S"] = "3"
+    d = _init(rank, ws, port)
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(1)
+    model = d.DDP(d.SimpleCNN().to(dev), device_ids=[rank], comm="p2p")
+    opt = d.SGD(model.parameters(), lr=0.01)
+    step = d.TrainStep(model, d.CrossEntropyLoss(), opt, cuda_graph=True)
+    g = torch.Generator(device="cpu").manual_seed(rank)
+    x = d.ops.preprocess_u8(torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).to(dev))
+    y = torch.randint(0, 10, (32,), generator=g).to(dev)
+    for _ in range(8):
+        step(x, y)
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == ws - 1:
+        os._exit(17)                                   # SIGKILL-like: no clean-up, no goodbye
+    t0 = time.time()
+    rec = {"raised": False}
+    try:
+        for _ in range(200):
+            step(x, y).item()
+            time.sleep(0.01)
+    except RuntimeError as e:
+        rec.update(raised=True, seconds=time.time() - t0, message=str(e)[:200])
+    torch.cuda.synchronize()
+    rec["gpu_alive"] = bool(torch.ones(4, device=dev).sum().item() == 4)
+    torch.save(rec, os.path.join(out_dir, f"dead{rank}.pt"))
+    os._exit(0)                                        # the process group has a dead member: skip the handshake
+
+
 def nvls_worker(rank, ws, port, out_dir):
-    """NVLS (multimem) all-reduce through the symm_mem-provided arena, where the box supports multicast."""
+    """NVLS (multimem) all-reduce through this framework's own multicast-bound arena (csrc/runtime/vmm_arena.cpp)."""
     d = _init(rank, ws, port)
     from distributeddataparallel_b200.parallel.p2p import P2PComm
 
@@ -177,7 +290,7 @@ def nvls_worker(rank, ws, port, out_dir):
     try:
         comm = P2PComm(None, dev, algo="nvls")
         comm.reserve(128 << 20)
-    except Exception as e:                      # symm_mem allocator unavailable on this box
+    except Exception as e:                      # neither the VMM nor the IPC arena could be set up
         rec["unavailable"] = repr(e)[:300]
         torch.save(rec, os.path.join(out_dir, f"nvls{rank}.pt"))
         d.cleanup()
@@ -192,7 +305,7 @@ def nvls_worker(rank, ws, port, out_dir):
             ref = src.float().clone()
             dist.all_reduce(ref)
             ref /= ws
-            for algo in ("nvls", "twoshot"):        # both kernels must work on the symm_mem arena
+            for algo in ("nvls", "twoshot"):        # both kernels must work on the multicast-bound arena
                 comm.algo = algo
                 flat.copy_(src)
                 comm.launch(0, flat, True).wait()

@@ -74,3 +74,119 @@ def test_bad_arguments_are_rejected():
         w.allreduce(8, 64, torch.float32, 2)        # offset not 16-byte aligned
     with pytest.raises(RuntimeError):
         w.allreduce(0, 64 << 20, torch.float32, 1)  # too large for one-shot
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_push_allreduce_single_exchange(world, dtype):
+    """Push kernel (one flag exchange, staging double-buffered on the epoch parity): several calls in a row, with other
+    collectives interleaved on the same channel, must keep giving the bit-identical average on every rank."""
+    from distributeddataparallel_b200.ops import native
+    import ctypes
+
+    lib = native.load_library()
+    lib.b200_allreduce_push_stage_bytes.restype = ctypes.c_size_t
+    lib.b200_allreduce_push_max_bytes.restype = ctypes.c_size_t
+    stage_bytes, max_bytes = lib.b200_allreduce_push_stage_bytes(), lib.b200_allreduce_push_max_bytes()
+    w = _world(world, arena_bytes=(8 << 20) + stage_bytes)
+    stage_off = 8 << 20
+    esize = 4 if dtype == torch.float32 else 2
+    g = torch.Generator(device="cpu").manual_seed(world)
+    off = 1024
+    for it, nbytes in enumerate((16, 37_632, 4096, max_bytes, 37_632, 37_632)):
+        numel = nbytes // esize
+        src = [torch.randn(numel, generator=g).to(dtype) for _ in range(world)]
+        for r in range(world):
+            w.view(r, off, numel, dtype).copy_(src[r])
+        w.allreduce_push(off, nbytes, dtype, stage_off)
+        if it % 2 == 1:
+            w.barrier(channel=0)              # another collective on the same flag rows in between
+        torch.cuda.synchronize()
+        assert w.error_word() == 0
+        outs = [w.view(r, off, numel, dtype).clone() for r in range(world)]
+        for o in outs[1:]:
+            assert torch.equal(o, outs[0])
+        ref = torch.stack([s.double() for s in src]).sum(0) / world
+        tol = 1e-6 if dtype == torch.float32 else 1e-2
+        assert torch.allclose(outs[0].double().cpu(), ref, rtol=tol, atol=tol)
+    with pytest.raises(RuntimeError):
+        w.allreduce_push(off, max_bytes + 16, dtype, stage_off)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("wire", [torch.bfloat16, torch.float16])
+def test_wire16_allreduce_fp32_data_16bit_wire(world, wire):
+    """fp32 buckets, 16-bit wire, fp32 accumulation: result = cast(sum_r cast(x_r / world)) within the wire precision,
+    bit-identical on every rank, and better than summing in the 16-bit type."""
+    w = _world(world, arena_bytes=32 << 20)
+    numel, off, stage = 1_000_000 // 8 * 8, 4096, 16 << 20
+    g = torch.Generator(device="cpu").manual_seed(3)
+    src = [torch.randn(numel, generator=g) for _ in range(world)]
+    for r in range(world):
+        w.view(r, off, numel, torch.float32).copy_(src[r])
+    w.allreduce_wire16(off, numel * 4, wire, stage)
+    torch.cuda.synchronize()
+    assert w.error_word() == 0
+    outs = [w.view(r, off, numel, torch.float32).clone() for r in range(world)]
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])
+    ref = torch.stack(src).double().sum(0) / world
+    err = float((outs[0].double().cpu() - ref).abs().max())
+    assert err < (4e-2 if wire == torch.bfloat16 else 6e-3), err
+    # exact model of the kernel: inputs rounded to the wire type, summed in fp32, rounded once more
+    model = torch.stack([(s / world).to(wire).float() for s in src]).sum(0).to(wire).float()
+    assert torch.allclose(outs[0].cpu(), model, rtol=0, atol=float(model.abs().max()) * 2 ** -7)
+
+
+def test_epoch_counters_wrap_around():
+    """Flags and epochs are compared with a signed difference: seed them just below 2^32 and cross the boundary."""
+    w = _world(4)
+    w.seed_epochs(2 ** 32 - 8)
+    numel, off = 8192, 0
+    for it in range(40):
+        for r in range(4):
+            w.view(r, off, numel, torch.float32).fill_(float(r + it))
+        w.allreduce(off, numel * 4, torch.float32, 1 + it % 2, scale=1.0)
+        if it % 3 == 0:
+            w.broadcast(1 << 20, 4096, it % 4, channel=0)
+    torch.cuda.synchronize()
+    assert w.error_word() == 0
+    assert int(w.epochs.view(torch.int32)[0]) > 0          # wrapped past zero
+    expect = float(sum(r + 39 for r in range(4)))
+    for r in range(4):
+        assert torch.all(w.view(r, off, numel, torch.float32) == expect)
+
+
+def test_dead_peer_times_out_poisons_and_raises_error_word():
+    """A rank whose peer never arrives must not hang and must not pass stale data off as a result: the wait is bounded
+    by the context's time limit, the error word is set and the local result is NaN."""
+    import ctypes
+    from distributeddataparallel_b200.ops import native
+    from distributeddataparallel_b200.parallel import p2p
+
+    lib = p2p._lib()
+    dev = torch.device("cuda")
+    arenas = [torch.zeros(8 << 20, dtype=torch.uint8, device=dev) for _ in range(2)]
+    pads = [torch.zeros(lib.b200_comm_signal_bytes() // 4, dtype=torch.int32, device=dev) for _ in range(2)]
+    epochs = torch.zeros(lib.b200_comm_epoch_bytes() // 4, dtype=torch.int32, device=dev)
+    error = torch.zeros(16, dtype=torch.int32).pin_memory()          # host-visible, as in the real arena
+    ctx = p2p._pack_ctx([a.data_ptr() for a in arenas], [p.data_ptr() for p in pads], epochs.data_ptr(),
+                        error.data_ptr(), 0, 2, 0, 0, 0, int(0.2e9))
+    data = arenas[0][:4096].view(torch.float32)
+    for algo in (1, 2):
+        data.fill_(1.0)
+        error.zero_()
+        native._call("b200_allreduce", ctx, ctypes.c_size_t(0), ctypes.c_size_t(4096), ctypes.c_int(0),
+                     ctypes.c_float(0.5), ctypes.c_int(algo), ctypes.c_int(4),
+                     ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()                        # returns: the spin is bounded (0.2 s)
+        assert (int(error[0]) & 0xFFFFFFFF) >> 16 == 0xDEAD
+        assert (int(error[0]) & 0xFFFF) == 1            # ... waiting for rank 1
+        assert torch.isnan(data).all()
+    stage_off = 2 << 20
+    data.fill_(1.0)
+    error.zero_()
+    native._call("b200_allreduce_push", ctx, ctypes.c_size_t(0), ctypes.c_size_t(4096), ctypes.c_int(0),
+                 ctypes.c_float(0.5), ctypes.c_size_t(stage_off), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert (int(error[0]) & 0xFFFFFFFF) >> 16 == 0xDEAD and torch.isnan(data).all()

@@ -45,8 +45,9 @@ def _rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-12))
 
 
-# (N, H, C, K, R, stride, pad): deep split-K (M = 32, 32 splits), mid split-K, and no split at all
-SHAPES = [(32, 1, 512, 512, 3, 1, 1), (32, 8, 64, 64, 3, 1, 1), (32, 32, 3, 64, 7, 2, 3)]
+# (N, H, C, K, R, stride, pad): deep split-K (M = 32, 32 splits), mid split-K, a 2-way split (128 tiles on 148
+# SMs), and no split at all (256 tiles: the scratch array is not touched)
+SHAPES = [(32, 1, 512, 512, 3, 1, 1), (32, 8, 64, 64, 3, 1, 1), (32, 32, 3, 64, 7, 2, 3), (64, 16, 16, 64, 3, 1, 1)]
 
 
 @pytest.mark.parametrize("shape", SHAPES)
