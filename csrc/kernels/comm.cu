@@ -70,6 +70,7 @@ struct CommCtx {
   int rank, world, channel, emulate;
   unsigned char* mc;                // NVLS: multicast mapping of the arenas (0 if the box has none)
   unsigned long long timeout_ns;    // bound on every wait (0: kDefaultTimeoutNs)
+  unsigned long long* stamps;       // optional: [0] = %globaltimer when block 0 starts, [1] = when it ends (device-timed logger)
 };
 
 __device__ __forceinline__ int ctx_rank(const CommCtx& c) { return c.emulate ? (int)blockIdx.y : c.rank; }
@@ -82,6 +83,11 @@ __device__ __forceinline__ unsigned long long global_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
+}
+
+// Device-side timestamps for the logger: free of extra launches, valid under CUDA-graph replay.
+__device__ __forceinline__ void stamp(const CommCtx& c, int which) {
+  if (c.stamps != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) c.stamps[which] = global_ns();
 }
 
 __device__ __forceinline__ void raise_error(const CommCtx& c, uint32_t code) {
@@ -195,6 +201,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
                                                                 float scale) {
   constexpr int NMAX = NR ? NR : kMaxRanks;
   const int rank = ctx_rank(c), N = NR ? NR : c.world;
+  stamp(c, 0);
   if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
@@ -223,6 +230,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
     }
   }
   if (!block_barrier(c, rank)) poison_local(c, rank, offset, nvec);
+  stamp(c, 1);
 }
 
 // ---- NVLS (in-switch reduction through the NVLink multicast mapping) ---------------------------------
@@ -259,6 +267,7 @@ template <> struct Multimem<__nv_bfloat16> {
 template <typename T>
 __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommCtx c, size_t offset, size_t nvec, float scale) {
   const int rank = ctx_rank(c), N = c.world;
+  stamp(c, 0);
   if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   const size_t per = (nvec + N - 1) / N;
   const size_t begin = min(nvec, (size_t)rank * per), end = min(nvec, begin + per);
@@ -282,6 +291,7 @@ __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommCtx c, si
   }
   __threadfence_system();
   if (!block_barrier(c, rank)) poison_local(c, rank, offset, nvec);
+  stamp(c, 1);
 }
 
 // ---- one-shot ------------------------------------------------------------------------------------
@@ -290,6 +300,7 @@ template <typename T>
 __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c, size_t offset, size_t nvec,
                                                                 float scale) {
   const int rank = ctx_rank(c), N = c.world;
+  stamp(c, 0);
   if (!block_barrier(c, rank)) return poison_local(c, rank, offset, nvec);
   uint4 res[kOneShotVecPerThread];
   const size_t base = (size_t)blockIdx.x * blockDim.x * kOneShotVecPerThread + threadIdx.x;
@@ -314,12 +325,14 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommCtx c,
     const size_t i = base + (size_t)k * blockDim.x;
     if (i < nvec) *reinterpret_cast<uint4*>(c.bufs[rank] + offset + i * 16) = res[k];
   }
+  stamp(c, 1);
 }
 
 // ---- broadcast (scatter from root + push all-gather) ------------------------------------------------
 __global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t offset, size_t nvec, int root) {
   constexpr int U = 8;
   const int rank = ctx_rank(c), N = c.world;
+  stamp(c, 0);
   if (!block_barrier(c, rank)) {
     if (rank != root) poison_local(c, rank, offset, nvec);
     return;
@@ -344,6 +357,7 @@ __global__ void __launch_bounds__(512) broadcast_kernel(const CommCtx c, size_t 
     }
   }
   if (!block_barrier(c, rank) && rank != root) poison_local(c, rank, offset, nvec);
+  stamp(c, 1);
 }
 
 __global__ void __launch_bounds__(32) barrier_kernel(const CommCtx c) { block_barrier(c, ctx_rank(c)); }
@@ -359,6 +373,7 @@ __global__ void __launch_bounds__(512) allreduce_push_kernel(const CommCtx c, si
                                                              size_t stage_off) {
   __shared__ int ok_s;
   const int rank = ctx_rank(c), N = c.world;
+  stamp(c, 0);
   const uint32_t epoch = next_epoch(c, rank);
   const size_t parity_off = stage_off + (size_t)(epoch & 1u) * kMaxRanks * kPushMaxBytes;
   const size_t base = (size_t)blockIdx.x * blockDim.x * kPushVecPerThread + threadIdx.x;
@@ -400,6 +415,7 @@ __global__ void __launch_bounds__(512) allreduce_push_kernel(const CommCtx c, si
     }
     *reinterpret_cast<uint4*>(c.bufs[rank] + offset + i * 16) = out;
   }
+  stamp(c, 1);
 }
 
 // ---- two-shot with a 16-bit wire format for fp32 data ----------------------------------------------------
@@ -427,6 +443,7 @@ __global__ void __launch_bounds__(512) allreduce_wire16_kernel(const CommCtx c, 
   const int rank = ctx_rank(c), N = c.world;
   const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   float* data = reinterpret_cast<float*>(c.bufs[rank] + offset);
+  stamp(c, 0);
   // 1. local cast into the staging object (pre-scaled by 1/world like the stock compress hooks: keeps fp16 in range)
   for (size_t i = tid; i < nw; i += stride) {
     const float4 lo = *reinterpret_cast<const float4*>(data + i * 8), hi = *reinterpret_cast<const float4*>(data + i * 8 + 4);
@@ -470,6 +487,7 @@ __global__ void __launch_bounds__(512) allreduce_wire16_kernel(const CommCtx c, 
     *reinterpret_cast<float4*>(data + i * 8) = make_float4(f0.x, f0.y, f1.x, f1.y);
     *reinterpret_cast<float4*>(data + i * 8 + 4) = make_float4(f2.x, f2.y, f3.x, f3.y);
   }
+  stamp(c, 1);
 }
 
 template <typename K, typename... Args>
@@ -528,7 +546,7 @@ B200_API int b200_allreduce(const void* ctx, size_t offset, size_t nbytes, int d
   }
   if (algo == 3) {          // NVLS
     if (c.mc == nullptr || c.emulate) return static_cast<int>(cudaErrorNotSupported);
-    const int nb = pick_blocks((nvec + c.world - 1) / c.world, min(max_blocks, 24));
+    const int nb = pick_blocks((nvec + c.world - 1) / c.world, max_blocks);      // the caller caps it (24 by default)
     if (dtype == 0) return launch_comm(allreduce_nvls_kernel<float>, c, nb, 512, stream, offset, nvec, scale);
     return launch_comm(allreduce_nvls_kernel<__nv_bfloat16>, c, nb, 512, stream, offset, nvec, scale);
   }
@@ -587,6 +605,18 @@ B200_API int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int r
   if (nvec == 0) return 0;
   const int blocks = pick_blocks((nvec + c.world - 1) / c.world, max(1, min(max_blocks, kMaxCommBlocks)));
   return launch_comm(broadcast_kernel, c, blocks, 512, stream, offset, nvec, root);
+}
+
+// 1-thread kernel that writes %globaltimer to *dst: the main-stream marks of the device-timed logger
+__global__ void stamp_kernel(unsigned long long* dst) {
+  pdl_launch_dependents();
+  pdl_wait();
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  *dst = t;
+}
+B200_API int b200_stamp(unsigned long long* dst, cudaStream_t stream) {
+  return static_cast<int>(launch_pdl(stamp_kernel, dim3(1), dim3(1), 0, stream, dst));
 }
 
 B200_API int b200_barrier(const void* ctx, cudaStream_t stream) {

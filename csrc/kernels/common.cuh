@@ -47,4 +47,35 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   return v;
 }
 
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------------
+// The training step is a chain of ~140 short kernels; between two dependent kernels the GPU otherwise idles for the
+// launch latency plus the next kernel's prologue (barrier init, TMEM allocation, descriptor prefetch).  Kernels
+// launched through launch_pdl() may become resident while their predecessor in the stream is still running:
+//   * pdl_launch_dependents() at the top of a kernel lets the NEXT kernel's CTAs be scheduled as soon as all of
+//     this kernel's CTAs have started;
+//   * pdl_wait() blocks until the PREVIOUS kernel has completed and its memory is visible.  Every kernel launched
+//     with the attribute must execute it before its first global-memory access (reads AND writes): that also keeps
+//     completion transitive along the chain.
+// Both are no-ops for a kernel launched the ordinary way.  CUDA graphs capture the attribute as a programmatic edge.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();      // defined in elementwise.cu (B200DDP_PDL=0 or b200_set_pdl(0) turns it off)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace b200

@@ -146,6 +146,8 @@ __global__ void __launch_bounds__(NT) conv_gemm_kernel(const ConvArgs g) {
   __shared__ float col_sum[BN], col_sq[BN];
   __shared__ unsigned ticket_s;
 
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = threadIdx.x;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   const int split = blockIdx.z;
@@ -336,10 +338,10 @@ __global__ void __launch_bounds__(NT) conv_gemm_kernel(const ConvArgs g) {
 
 template <int MODE>
 static int launch_mode(const ConvArgs& g, dim3 grid, bool vec_a, bool vec_b, cudaStream_t st) {
-  if (vec_a && vec_b) conv_gemm_kernel<MODE, true, true><<<grid, NT, 0, st>>>(g);
-  else if (vec_a) conv_gemm_kernel<MODE, true, false><<<grid, NT, 0, st>>>(g);
-  else if (vec_b) conv_gemm_kernel<MODE, false, true><<<grid, NT, 0, st>>>(g);
-  else conv_gemm_kernel<MODE, false, false><<<grid, NT, 0, st>>>(g);
+  if (vec_a && vec_b) (void)launch_pdl(conv_gemm_kernel<MODE, true, true>, grid, dim3(NT), 0, st, g);
+  else if (vec_a) (void)launch_pdl(conv_gemm_kernel<MODE, true, false>, grid, dim3(NT), 0, st, g);
+  else if (vec_b) (void)launch_pdl(conv_gemm_kernel<MODE, false, true>, grid, dim3(NT), 0, st, g);
+  else (void)launch_pdl(conv_gemm_kernel<MODE, false, false>, grid, dim3(NT), 0, st, g);
   return static_cast<int>(cudaPeekAtLastError());
 }
 

@@ -1,16 +1,28 @@
 // Small elementwise kernels: input pipeline, scaling, accumulation.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "b200ddp.h"
 
 namespace b200 {
 
+static int g_pdl = -1;       // -1: read B200DDP_PDL on first use (default on)
+bool pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("B200DDP_PDL");
+    g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl != 0;
+}
+
 // uint8 NHWC -> fp32 NHWC with torchvision's ToTensor + Normalize(mean, std) arithmetic
 // (/root/reference/dpp.py:32): (x / 255 - mean) / std, same operation order, so values match
 // the reference's host-side transform bit for bit.
 __global__ void __launch_bounds__(256) preprocess_u8_kernel(const uint8_t* __restrict__ in, float* __restrict__ out,
                                                             size_t n, float mean, float stdv) {
+  pdl_launch_dependents();
+  pdl_wait();
   const size_t n4 = n / 4;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const uchar4 u = reinterpret_cast<const uchar4*>(in)[i];
@@ -30,6 +42,8 @@ __global__ void __launch_bounds__(256) preprocess_u8_kernel(const uint8_t* __res
 // out = a * (*scale_dev or scale_host)
 __global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ a, float* __restrict__ out, size_t n,
                                                     const float* __restrict__ scale_dev, float scale_host) {
+  pdl_launch_dependents();
+  pdl_wait();
   const float s = scale_dev ? __ldg(scale_dev) * scale_host : scale_host;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = a[i] * s;
@@ -206,15 +220,16 @@ static int grid1d(size_t n, int per_thread = 4) {
 
 using namespace b200;
 
+// Programmatic dependent launch on/off for every kernel of the library (default on; see common.cuh).
+B200_API void b200_set_pdl(int enabled) { b200::g_pdl = enabled ? 1 : 0; }
+
 B200_API int b200_preprocess_u8(const uint8_t* in, float* out, size_t n, float mean, float stdv, cudaStream_t stream) {
-  preprocess_u8_kernel<<<grid1d(n / 4 + 1, 2), 256, 0, stream>>>(in, out, n, mean, stdv);
-  B200_LAUNCH_CHECK();
+  return static_cast<int>(launch_pdl(preprocess_u8_kernel, dim3(grid1d(n / 4 + 1, 2)), dim3(256), 0, stream, in, out, n, mean, stdv));
 }
 
 B200_API int b200_scale(const float* a, float* out, size_t n, const float* scale_dev, float scale_host,
                         cudaStream_t stream) {
-  scale_kernel<<<grid1d(n), 256, 0, stream>>>(a, out, n, scale_dev, scale_host);
-  B200_LAUNCH_CHECK();
+  return static_cast<int>(launch_pdl(scale_kernel, dim3(grid1d(n)), dim3(256), 0, stream, a, out, n, scale_dev, scale_host));
 }
 
 B200_API int b200_add(const float* a, const float* b, float* out, size_t n, cudaStream_t stream) {

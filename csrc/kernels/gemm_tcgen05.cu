@@ -346,6 +346,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   __shared__ uint32_t tmem_base_s;
   __shared__ unsigned ticket_s;
 
+  pdl_launch_dependents();            // the next kernel in the stream may set up while this one runs (common.cuh)
   const int t = threadIdx.x, warp = t >> 5;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   const int zb = a.batch > 1 ? (int)blockIdx.z : 0;                 // batch index (no split-K when batched)
@@ -355,7 +356,10 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   const char* b_base = static_cast<const char*>(a.b) + (zo * a.b_s0 + zi * a.b_s1) * ES;
   float* out_base = reinterpret_cast<float*>(reinterpret_cast<char*>(a.out) +
                                              (zo * a.o_s0 + zi * a.o_s1) * (a.out_bf16 ? 2 : 4));
-  if (a.causal == 1 && n0 >= m0 + BM) return;                      // whole tile masked: nothing reads it
+  if (a.causal == 1 && n0 >= m0 + BM) {                            // whole tile masked: nothing reads it
+    pdl_wait();                                                    // (still a link of the completion chain)
+    return;
+  }
   int k_begin = split_z * a.k_per_split;
   int k_end = min(a.Kd, k_begin + a.k_per_split);
   if (a.causal == 2) k_end = min(k_end, m0 + BM);                   // keys beyond the last query row of the tile are masked
@@ -386,6 +390,9 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   if (a.cluster_reduce) cluster_sync_all();                 // every CTA's cl_* barriers exist before anyone signals them
   tc_fence_after();
   const uint32_t tmem_d = tmem_base_s;
+  // everything above (barrier init, TMEM allocation, descriptor prefetch) touched no global memory and may have
+  // overlapped the previous kernel; from here on its results are needed
+  pdl_wait();
 
   if (warp < 8) {
     // ================= producers =================
@@ -1349,8 +1356,12 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     attr.val.clusterDim.x = 1;
     attr.val.clusterDim.y = 1;
     attr.val.clusterDim.z = grid.z;
-    cfg.attrs = &attr;
-    cfg.numAttrs = 1;
+    cudaLaunchAttribute attrs[2];
+    attrs[0] = attr;
+    attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attrs;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     static bool big_clusters = false;   // per template instantiation
     if (grid.z > 8 && !big_clusters) {
       cudaError_t e2 = cudaFuncSetAttribute(gemm_kernel<AK, BK_, BN, BF16>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
@@ -1361,7 +1372,10 @@ static int launch(const Args& a_in, dim3 grid, cudaStream_t st) {
     if (e != cudaSuccess) return static_cast<int>(e);
     return static_cast<int>(cudaPeekAtLastError());
   }
-  gemm_kernel<AK, BK_, BN, BF16><<<grid, THREADS, smem, st>>>(a, map_a, map_b);
+  {
+    cudaError_t e = launch_pdl(gemm_kernel<AK, BK_, BN, BF16>, grid, dim3(THREADS), (size_t)smem, st, a, map_a, map_b);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  }
   return static_cast<int>(cudaPeekAtLastError());
 }
 

@@ -61,6 +61,8 @@ __global__ void __launch_bounds__(1024) softmax_xent_small_kernel(const float* _
                                                                   const long long* __restrict__ target,
                                                                   float* __restrict__ loss,
                                                                   float* __restrict__ dlogits, int B, int V) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float sh[32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float my = 0.f;
@@ -94,7 +96,7 @@ using namespace b200;
 B200_API int b200_softmax_xent(const float* logits, const long long* target, float* loss, float* dlogits,
                                float* row_loss_scratch, int B, int V, cudaStream_t stream) {
   if (B <= 32 && dlogits != nullptr) {
-    softmax_xent_small_kernel<<<1, 1024, 0, stream>>>(logits, target, loss, dlogits, B, V);
+    (void)launch_pdl(softmax_xent_small_kernel, dim3(1), dim3(1024), 0, stream, logits, target, loss, dlogits, B, V);
     B200_LAUNCH_CHECK();
   }
   const int warps = 8;

@@ -31,6 +31,8 @@ struct ChunkRec { int tensor; int chunk; };
 //                        Adam [lr, beta1, beta2, eps, weight_decay, decoupled, maximize, grad_scale, step]
 __global__ void __launch_bounds__(256) sgd_kernel(const TensorRec* __restrict__ recs, const ChunkRec* __restrict__ chunks,
                                                   const float* __restrict__ hyper) {
+  pdl_launch_dependents();
+  pdl_wait();
   const ChunkRec ch = chunks[blockIdx.x];
   const TensorRec r = recs[ch.tensor];
   const float lr = hyper[0], mom = hyper[1], damp = hyper[2], wd = hyper[3];
@@ -154,8 +156,8 @@ B200_API int b200_optim_rec_bytes() { return (int)sizeof(TensorRec); }
 B200_API int b200_fused_sgd(const void* recs, const void* chunks, int num_chunks, const float* hyper,
                             cudaStream_t stream) {
   if (num_chunks <= 0) return 0;
-  sgd_kernel<<<num_chunks, 256, 0, stream>>>(static_cast<const TensorRec*>(recs), static_cast<const ChunkRec*>(chunks), hyper);
-  B200_LAUNCH_CHECK();
+  return static_cast<int>(launch_pdl(sgd_kernel, dim3(num_chunks), dim3(256), 0, stream, static_cast<const TensorRec*>(recs),
+                                     static_cast<const ChunkRec*>(chunks), hyper));
 }
 
 B200_API int b200_fused_adam(const void* recs, const void* chunks, int num_chunks, float* hyper,

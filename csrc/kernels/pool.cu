@@ -13,6 +13,8 @@ namespace b200 {
 __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                                uint8_t* __restrict__ idx, int Nb, int H, int W, int C,
                                                                int P, int Q) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int c4n = C >> 2;
   const size_t total = (size_t)Nb * P * Q * c4n;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -50,6 +52,8 @@ __global__ void __launch_bounds__(256) maxpool3x3s2_fwd_kernel(const float* __re
 __global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const float* __restrict__ dy,
                                                                const uint8_t* __restrict__ idx, float* __restrict__ dx,
                                                                int Nb, int H, int W, int C, int P, int Q) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int c4n = C >> 2;
   const size_t total = (size_t)Nb * H * W * c4n;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -118,16 +122,16 @@ B200_API int b200_maxpool3x3s2_fwd(const float* x, float* y, uint8_t* idx, int N
                                    cudaStream_t stream) {
   if (C % 4) return static_cast<int>(cudaErrorInvalidValue);
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
-  maxpool3x3s2_fwd_kernel<<<grid1d((size_t)Nb * P * Q * C / 4), 256, 0, stream>>>(x, y, idx, Nb, H, W, C, P, Q);
-  B200_LAUNCH_CHECK();
+  return static_cast<int>(launch_pdl(maxpool3x3s2_fwd_kernel, dim3(grid1d((size_t)Nb * P * Q * C / 4)), dim3(256), 0, stream,
+                                     x, y, idx, Nb, H, W, C, P, Q));
 }
 
 B200_API int b200_maxpool3x3s2_bwd(const float* dy, const uint8_t* idx, float* dx, int Nb, int H, int W, int C,
                                    cudaStream_t stream) {
   if (C % 4) return static_cast<int>(cudaErrorInvalidValue);
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
-  maxpool3x3s2_bwd_kernel<<<grid1d((size_t)Nb * H * W * C / 4), 256, 0, stream>>>(dy, idx, dx, Nb, H, W, C, P, Q);
-  B200_LAUNCH_CHECK();
+  return static_cast<int>(launch_pdl(maxpool3x3s2_bwd_kernel, dim3(grid1d((size_t)Nb * H * W * C / 4)), dim3(256), 0, stream,
+                                     dy, idx, dx, Nb, H, W, C, P, Q));
 }
 
 B200_API int b200_avgpool_fwd(const float* x, float* y, int Nb, int HW, int C, cudaStream_t stream) {

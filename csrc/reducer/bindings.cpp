@@ -34,6 +34,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("set_require_sync", &Reducer::set_require_sync)
       .def("require_sync", &Reducer::require_sync)
       .def("set_comm", &Reducer::set_comm)
+      .def("set_backward_end_callback", &Reducer::set_backward_end_callback)
       .def("detach_hooks", &Reducer::detach_hooks)
       .def("attach_hooks", &Reducer::attach_hooks)
       .def("num_buckets", &Reducer::num_buckets)

@@ -242,6 +242,7 @@ Reducer::~Reducer() {
   for (auto& b : buckets_) b.handle = py::object();
   comm_ = py::object();
   allocator_ = py::object();
+  backward_end_cb_ = py::object();
 }
 
 void Reducer::detach_hooks() {
@@ -475,6 +476,7 @@ void Reducer::finalize_backward() {
   }
   {
     py::gil_scoped_acquire gil;
+    if (backward_end_cb_ && !backward_end_cb_.is_none()) backward_end_cb_();
     for (auto& b : buckets_) {
       if (b.handle && !b.handle.is_none()) b.handle.attr("wait")();
       b.handle = py::object();

@@ -97,6 +97,9 @@ class Reducer {
   void set_require_sync(bool v) { require_sync_ = v; }
   bool require_sync() const { return require_sync_; }
   void set_comm(py::object comm) { comm_ = std::move(comm); }
+  // Called (with the GIL) at the end of the backward pass, before the bucket handles are waited on: the device-timed
+  // logger stamps "backward compute done" there; the gap to the last bucket's end stamp is the exposed communication.
+  void set_backward_end_callback(py::object cb) { backward_end_cb_ = std::move(cb); }
   void detach_hooks();
   // (Re)create the gradient-accumulator nodes under the CURRENT stream and hook them.  Needed
   // before capturing a step into a CUDA graph on a side stream: autograd pins an accumulator
@@ -138,6 +141,7 @@ class Reducer {
   std::vector<Bucket> buckets_;
   py::object comm_;
   py::object allocator_;
+  py::object backward_end_cb_;
   int64_t world_size_;
   bool grad_as_view_;
   bool find_unused_;

@@ -70,6 +70,8 @@ class TrainStep:
             torch.cuda.nvtx.range_pop()
             torch.cuda.nvtx.range_push("b200ddp.optimizer")
         self.optimizer.step()
+        if self._ddp is not None:
+            self._ddp._mark(self._ddp.STEP_END)
         if nvtx:
             torch.cuda.nvtx.range_pop()
         self.eager_steps += 1
@@ -111,6 +113,8 @@ class TrainStep:
                 loss = self._forward_loss(static_x, static_y)
                 loss.backward()
                 self.optimizer.step()
+                if self._ddp is not None:
+                    self._ddp._mark(self._ddp.STEP_END)
                 # drop the autograd graph now: it keeps the capture-stream accumulator nodes alive
                 loss = loss.detach()
         finally:

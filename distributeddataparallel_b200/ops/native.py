@@ -446,6 +446,11 @@ def _conv_call(name: str, head: tuple, geom: tuple, dev: torch.device, acts=()) 
     ffma_launches += 1
 
 
+def stamp(ptr: int) -> None:
+    """Write %globaltimer (ns) to the 64-bit word at device address ``ptr`` on the current stream."""
+    _call("b200_stamp", ctypes.c_void_p(ptr), _stream())
+
+
 def tc_error_word(device=None) -> int:
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     idx = dev.index if dev.index is not None else torch.cuda.current_device()
@@ -595,6 +600,27 @@ def conv2d(x, w, stride: int, padding: int, stats: Optional[torch.Tensor] = None
 # batch norm (+ residual) (+ relu)
 # ---------------------------------------------------------------------------------------
 _FUSED_BN_BWD = _os.environ.get("B200DDP_FUSED_BN_BWD", "0") != "0"   # measured: no gain (step is not launch bound)
+# Cluster BatchNorm kernels (one launch per direction, deterministic) for tensors of <= 131 072 elements:
+#   backward: on by default (one kernel instead of reduce + apply on the backward critical path);
+#   forward : B200DDP_BN_STATS=exact computes exact two-pass statistics in the BatchNorm kernel itself instead of taking
+#             the float-atomic sums of the convolution epilogue (bit-reproducible, robust for |mean| >> std).
+_DETERMINISTIC = _os.environ.get("B200DDP_DETERMINISTIC", "0") != "0"
+_BN_CLUSTER_BWD = _os.environ.get("B200DDP_BN_CLUSTER", "1" if _DETERMINISTIC else "0") != "0"
+_BN_STATS_MODE = _os.environ.get("B200DDP_BN_STATS", "exact" if _DETERMINISTIC else "fused")          # fused | exact
+
+
+def set_bn_stats_mode(mode: str) -> None:
+    global _BN_STATS_MODE
+    assert mode in ("fused", "exact")
+    _BN_STATS_MODE = mode
+
+
+def bn_stats_mode() -> str:
+    return _BN_STATS_MODE
+
+
+def _cluster_bn_ok(m: int, c: int) -> bool:
+    return c % 4 == 0 and m * c <= 131072 and (c // 4) <= 512 and 512 % (c // 4) == 0
 
 
 class BNWorkspace:
@@ -633,12 +659,17 @@ class _BatchNormAct(torch.autograd.Function):
         out = _empty_nhwc(n, c, h, w, x.device)
         save_mean = torch.empty(c, dtype=torch.float32, device=x.device)
         save_invstd = torch.empty(c, dtype=torch.float32, device=x.device)
-        if training and not stats_ready:
-            _call("b200_bn_stats", _ptr(xc), _ptr(ws.fwd), _i(m), _i(c), _stream())
-        _call("b200_bn_fwd_apply", _ptr(xc), _ptr(ws.fwd), _ptr(gamma), _ptr(beta), _ptr(res), _ptr(out),
-              _ptr(rmean), _ptr(rvar), _ptr(nbt), _ptr(save_mean), _ptr(save_invstd),
-              _ptr(ws.bwd), _i(ws.bwd.numel()), _i(m), _i(c), _f(momentum), _f(eps), _i(int(relu)),
-              _i(int(training)), _stream())
+        if training and not stats_ready and _BN_STATS_MODE == "exact" and _cluster_bn_ok(m, c):
+            _call("b200_bn_fwd_cluster", _ptr(xc), _ptr(gamma), _ptr(beta), _ptr(res), _ptr(out), _ptr(rmean), _ptr(rvar),
+                  _ptr(nbt), _ptr(save_mean), _ptr(save_invstd), _ptr(ws.bwd), _i(ws.bwd.numel()), _i(m), _i(c),
+                  _f(momentum), _f(eps), _i(int(relu)), _stream())
+        else:
+            if training and not stats_ready:
+                _call("b200_bn_stats", _ptr(xc), _ptr(ws.fwd), _i(m), _i(c), _stream())
+            _call("b200_bn_fwd_apply", _ptr(xc), _ptr(ws.fwd), _ptr(gamma), _ptr(beta), _ptr(res), _ptr(out),
+                  _ptr(rmean), _ptr(rvar), _ptr(nbt), _ptr(save_mean), _ptr(save_invstd),
+                  _ptr(ws.bwd), _i(ws.bwd.numel()), _i(m), _i(c), _f(momentum), _f(eps), _i(int(relu)),
+                  _i(int(training)), _stream())
         ws.bwd_dirty = False
         ctx.save_for_backward(xc, out if relu else None, gamma, save_mean, save_invstd)
         ctx.cfg = (m, c, bool(relu), residual is not None, training)
@@ -665,7 +696,11 @@ class _BatchNormAct(torch.autograd.Function):
         dres = torch.empty_like(xc, memory_format=torch.preserve_format) if has_res else None
         dgamma, _ = _grad_target(ctx.params[0], ctx.slots[0], gamma)
         dbeta, _ = _grad_target(ctx.params[1], ctx.slots[1], gamma)
-        if _FUSED_BN_BWD:
+        if _BN_CLUSTER_BWD and _cluster_bn_ok(m, c):
+            _call("b200_bn_bwd_cluster", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean), _ptr(save_invstd),
+                  _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0), _ptr(ws.fwd), _i(ws.fwd.numel()), _i(m), _i(c),
+                  _i(int(relu)), _stream())
+        elif _FUSED_BN_BWD:
             _call("b200_bn_bwd_fused", _ptr(dout), _ptr(out), _ptr(xc), _ptr(gamma), _ptr(save_mean),
                   _ptr(save_invstd), _ptr(ws.bwd), _ptr(dx), _ptr(dres), _ptr(dgamma), _ptr(dbeta), _i(0),
                   _ptr(ws.fwd), _i(ws.fwd.numel()), _ptr(ws.tickets), _i(m), _i(c), _i(int(relu)), _stream())
@@ -694,6 +729,15 @@ def conv_bn_act(x, conv_weight, stride, padding, bn, residual=None, relu=False):
     """conv -> BN(+residual)(+ReLU) with the BN statistics accumulated by the conv epilogue."""
     training = bn.training or not bn.track_running_stats
     ws = bn_workspace(bn, conv_weight.shape[0], x.device)
+    if training and _BN_STATS_MODE == "exact":
+        # statistics are computed by the BatchNorm kernel itself (exact two-pass, deterministic): the convolution
+        # epilogue accumulates nothing
+        y = conv2d(x, conv_weight, stride, padding, None)
+        return batch_norm_act(
+            y, bn.weight, bn.bias, bn.running_mean if bn.track_running_stats else None,
+            bn.running_var if bn.track_running_stats else None,
+            bn.num_batches_tracked if (bn.training and bn.track_running_stats) else None,
+            residual, relu, training, 0.1 if bn.momentum is None else bn.momentum, bn.eps, ws, stats_ready=False)
     if training:
         ws.begin_forward()
     y = conv2d(x, conv_weight, stride, padding, ws.fwd if training else None)

@@ -32,7 +32,9 @@ What is different by design:
 from __future__ import annotations
 
 import contextlib
+import os
 import sys
+import weakref
 from typing import Callable, List, Optional, Sequence
 
 import torch
@@ -104,6 +106,8 @@ class DistributedDataParallel(nn.Module):
         self._rebuilt_bucket_sizes: List[int] = []
         self._graph_mode = False
         self._buffers_ahead = False        # rank 0's buffers for the next forward were already broadcast
+        self._timing = False               # device-timed logger marks (enable_device_timing)
+        self._marks = None
 
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
@@ -128,11 +132,13 @@ class DistributedDataParallel(nn.Module):
             self.first_bucket_bytes, self.bucket_bytes_cap)
         self._initial_bucket_sizes = list(self.reducer.bucket_sizes())
         self._publish_grad_slots()
+        me = weakref.ref(self)
+        self.reducer.set_backward_end_callback(lambda: me() is not None and me()._mark(2))
+        if os.environ.get("B200DDP_DEVICE_TIMING", "0") != "0":
+            self.enable_device_timing()
         if self._comm.name == "p2p" and self.world_size > 1:
             # stream the last bucket (the one whose final gradient is the stem's weight gradient): pieces are
             # reduced as they become ready, the last few KB go through the single-exchange push kernel
-            import os
-
             spec = os.environ.get("B200DDP_TAIL_SPLITS", f"{1 << 20},{64 << 10}")
             self.reducer.set_tail_splits([int(v) for v in spec.split(",") if v.strip()])
 
@@ -309,11 +315,65 @@ class DistributedDataParallel(nn.Module):
                 self._collectives["broadcast"] += broadcast_coalesced(
                     self._comm, self._buffers_for_sync, self.broadcast_bucket_size, src=self._buffer_src)
 
+    # -- device-timed logger ---------------------------------------------------------------
+    FWD_START, BWD_START, BWD_END, STEP_END = 0, 1, 2, 3
+
+    def enable_device_timing(self, on: bool = True) -> None:
+        """Stamp %globaltimer on the training stream at forward start / backward start / backward end (and step end,
+        by ``TrainStep``).  The marks are 1-thread kernels, so they are captured in a step graph and keep working
+        under replay -- enable BEFORE the step is captured.  The collective kernels stamp their own start / end for
+        free; together they give device-timed forward / backward / communication / exposed-communication figures
+        (``device_timing()``, ``--print-ddp-stats``), replacing host clocks that measure nothing under a CUDA graph."""
+        self._timing = bool(on) and self.device.type == "cuda"
+        if self._timing and self._marks is None:
+            self._marks = torch.zeros(8, dtype=torch.int64, device=self.device)
+
+    def _mark(self, slot: int) -> None:
+        if self._timing:
+            from ..ops import native
+
+            native.stamp(self._marks.data_ptr() + 8 * slot)
+
+    def device_timing(self) -> dict:
+        """Figures of the LAST step, from device time stamps (synchronises): forward_us, backward_us, comm_span_us,
+        exposed_comm_us (= last bucket reduction end - backward compute end, clamped at 0), exposed_comm_pct of the
+        step, and per-launch-unit duration / bus GB/s."""
+        out: dict = {}
+        comm = self._comm
+        while getattr(comm, "inner", None) is not None:
+            comm = comm.inner
+        times = comm.device_times() if hasattr(comm, "device_times") else {"units": []}
+        out["units"] = [{k: u[k] for k in ("unit", "bytes", "us", "bus_gbs")} for u in times["units"]]
+        if "buffer_broadcast" in times:
+            out["buffer_broadcast_us"] = times["buffer_broadcast"]["us"]
+        if self._marks is None:
+            return out
+        torch.cuda.synchronize(self.device)
+        m = self._marks.cpu().tolist()
+        f0, b0, b1, s1 = m[self.FWD_START], m[self.BWD_START], m[self.BWD_END], m[self.STEP_END]
+        if f0 and b0 >= f0:
+            out["forward_us"] = (b0 - f0) / 1e3
+        if b0 and b1 >= b0:
+            out["backward_us"] = (b1 - b0) / 1e3
+        if f0 and s1 > f0:
+            out["step_us"] = (s1 - f0) / 1e3
+        this_step = [u for u in times["units"] if b0 and u["start_ns"] >= b0 and (not s1 or s1 < b0 or u["end_ns"] <= s1 + 10_000_000)]
+        if this_step and b1:
+            first, last = min(u["start_ns"] for u in this_step), max(u["end_ns"] for u in this_step)
+            out["comm_span_us"] = (last - first) / 1e3
+            out["comm_busy_us"] = sum(u["us"] for u in this_step)
+            out["exposed_comm_us"] = max(0.0, (last - b1) / 1e3)
+            if "step_us" in out and out["step_us"] > 0:
+                out["exposed_comm_pct"] = 100.0 * out["exposed_comm_us"] / out["step_us"]
+        return out
+
     def forward(self, *inputs, **kwargs):
         with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
             self._pre_forward()
+            self._mark(self.FWD_START)
             out = self.module(*inputs, **kwargs)
             self._post_forward()
+            self._mark(self.BWD_START)
             if torch.is_grad_enabled():
                 for p in self._params:
                     p._slot_claimed = False      # one in-place writer per parameter per backward (ops/native.py)

@@ -43,10 +43,10 @@ def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
 
 
 def _pack_ctx(bufs: Sequence[int], flags: Sequence[int], epochs: int, error: int, rank: int, world: int,
-              channel: int, emulate: int, multicast: int = 0, timeout_ns: int = 0) -> ctypes.Array:
+              channel: int, emulate: int, multicast: int = 0, timeout_ns: int = 0, stamps: int = 0) -> ctypes.Array:
     b = list(bufs) + [0] * (8 - len(bufs))
     f = list(flags) + [0] * (8 - len(flags))
-    raw = struct.pack("<8Q8QQQ4iQQ", *b, *f, epochs, error, rank, world, channel, emulate, multicast, timeout_ns)
+    raw = struct.pack("<8Q8QQQ4iQQQ", *b, *f, epochs, error, rank, world, channel, emulate, multicast, timeout_ns, stamps)
     lib = native.load_library()
     assert len(raw) == lib.b200_comm_ctx_bytes(), (len(raw), lib.b200_comm_ctx_bytes())
     return ctypes.create_string_buffer(raw, len(raw))
@@ -220,11 +220,14 @@ class SymmetricArena:
         self._ctx: Dict[int, ctypes.Array] = {}
         dist.barrier(group=group)      # everyone has mapped everyone before the first kernel
 
-    def ctx(self, channel: int) -> ctypes.Array:
-        c = self._ctx.get(channel)
+    def ctx(self, channel: int, stamps: int = 0) -> ctypes.Array:
+        """Host copy of the kernels' context for one channel; ``stamps`` = device address of a (start, end) pair of
+        64-bit words the collective writes %globaltimer into (device-timed logger), 0 for none."""
+        c = self._ctx.get((channel, stamps))
         if c is None:
-            c = self._ctx[channel] = _pack_ctx(self.peer_base, self.peer_base, self.epochs_ptr, self.error_ptr,
-                                               self.rank, self.world, channel, 0, self.multicast, self.timeout_ns)
+            c = self._ctx[(channel, stamps)] = _pack_ctx(self.peer_base, self.peer_base, self.epochs_ptr, self.error_ptr,
+                                                         self.rank, self.world, channel, 0, self.multicast,
+                                                         self.timeout_ns, stamps)
         return c
 
     def set_timeout(self, seconds: float) -> None:
@@ -295,6 +298,9 @@ class P2PComm(CommBase):
         self.algo = algo
         self.max_blocks = int(max_blocks or os.environ.get("B200DDP_COMM_BLOCKS", 32))
         self.last_blocks = int(os.environ.get("B200DDP_COMM_BLOCKS_LAST", self.max_blocks))
+        self.nvls_blocks = int(os.environ.get("B200DDP_NVLS_BLOCKS", 24))     # the switch reduces: few SMs suffice
+        self.nvls_min_world = int(os.environ.get("B200DDP_NVLS_MIN_WORLD", 4))
+        self.nvls_min_bytes = int(os.environ.get("B200DDP_NVLS_MIN_BYTES", 1 << 20))
         self.oneshot_max = int(os.environ.get("B200DDP_ONESHOT_MAX_BYTES", 256 << 10))
         self._arena_bytes = arena_bytes
         self.arena: Optional[SymmetricArena] = None
@@ -304,6 +310,10 @@ class P2PComm(CommBase):
         self._push_stage: Dict[int, int] = {}      # channel -> arena offset of the push all-reduce staging object
         self._buffer_region = None
         self._ahead_event: Optional[torch.cuda.Event] = None
+        # device-timed logger: (start, end) %globaltimer pair per launch unit + one for the buffer broadcast
+        self.MAX_STAMPED = 64
+        self._stamps = torch.zeros(2 * (self.MAX_STAMPED + 1), dtype=torch.int64, device=device)
+        self._stamp_bytes: Dict[int, int] = {}
         self.bytes_reduced = 0
         self.algo_counts: Dict[str, int] = {}
         # observability / safety switches
@@ -365,19 +375,30 @@ class P2PComm(CommBase):
         if self.algo == "auto":
             if nbytes <= min(self.oneshot_max, self.push_max):
                 return 4
-            if self.arena is not None and self.arena.multicast and nbytes >= (256 << 10):
+            # NVLS pays off where the switch saves link traffic: from 4 ranks up (on 2 ranks the two-shot kernel moves
+            # S/2 per direction and is faster: 32 MB 67 us vs 106 us measured)
+            if self.arena is not None and self.arena.multicast and self.world_size >= self.nvls_min_world \
+                    and nbytes >= self.nvls_min_bytes:
                 return 3
         return 2
 
+    def _stamp_ptr(self, unit: Optional[int]) -> int:
+        if unit is None or not (0 <= unit <= self.MAX_STAMPED):
+            return 0
+        return self._stamps.data_ptr() + 16 * unit
+
     def _allreduce_on(self, stream: torch.cuda.Stream, channel: int, off: int, nbytes: int, dtype: torch.dtype,
-                      blocks: Optional[int] = None, algo: Optional[int] = None) -> int:
+                      blocks: Optional[int] = None, algo: Optional[int] = None, unit: Optional[int] = None) -> int:
         algo = self._pick_algo(nbytes) if algo is None else algo
+        stamps = self._stamp_ptr(unit)
         if algo == 4:
-            native._call("b200_allreduce_push", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
+            native._call("b200_allreduce_push", self.arena.ctx(channel, stamps), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
                          ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
                          ctypes.c_size_t(self._push_stage[channel]), ctypes.c_void_p(stream.cuda_stream))
             return algo
-        native._call("b200_allreduce", self.arena.ctx(channel), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
+        if algo == 3:
+            blocks = min(blocks or self.nvls_blocks, self.nvls_blocks)
+        native._call("b200_allreduce", self.arena.ctx(channel, stamps), ctypes.c_size_t(off), ctypes.c_size_t(nbytes),
                      ctypes.c_int(_DTYPE_CODE[dtype]), ctypes.c_float(1.0 / self.divisor),
                      ctypes.c_int(algo), ctypes.c_int(blocks or self.max_blocks),
                      ctypes.c_void_p(stream.cuda_stream))
@@ -415,12 +436,14 @@ class P2PComm(CommBase):
         for ev in native.side_stream_events():        # weight gradients produced on the side streams (ops/native.py)
             self.stream.wait_event(ev)
         if wire is not None and flat.dtype == torch.float32 and nbytes % 32 == 0 and nbytes > self.push_max:
-            self.allreduce_wire16_(flat, wire, stream=self.stream, channel=self.GRAD_CHANNEL)
+            self.allreduce_wire16_(flat, wire, stream=self.stream, channel=self.GRAD_CHANNEL, unit=index)
             name = "wire16"
         else:
             algo = self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype,
-                                      blocks=self.last_blocks if is_last else None)
+                                      blocks=self.last_blocks if is_last else None, unit=index)
             name = self.ALGO_NAMES[algo]
+        if 0 <= index < self.MAX_STAMPED:
+            self._stamp_bytes[index] = nbytes
         self.algo_counts[name] = self.algo_counts.get(name, 0) + 1
         done = torch.cuda.Event(enable_timing=t0 is not None)
         done.record(self.stream)
@@ -489,6 +512,25 @@ class P2PComm(CommBase):
         f = 2 * (self.world_size - 1) / self.world_size
         return {"bytes": nbytes, "us": round(us, 2), "bus_gbs": round(nbytes * f / (us * 1e-6) / 1e9, 1),
                 "algo": self.ALGO_NAMES[algo]}
+
+    def device_times(self) -> dict:
+        """Device-side (start, end) of the last reduction of every launch unit and of the buffer broadcast, in ns of
+        %globaltimer (written by the kernels themselves: valid under CUDA-graph replay).  Synchronises."""
+        torch.cuda.synchronize(self.device)
+        st = self._stamps.cpu().tolist()
+        f = 2 * (self.world_size - 1) / max(self.world_size, 1)
+        units = []
+        for i in sorted(self._stamp_bytes):
+            a, b = st[2 * i], st[2 * i + 1]
+            if a and b and b >= a:
+                nb = self._stamp_bytes[i]
+                units.append({"unit": i, "bytes": nb, "start_ns": a, "end_ns": b, "us": (b - a) / 1e3,
+                              "bus_gbs": nb * f / max(b - a, 1)})
+        out = {"units": units}
+        a, b = st[2 * self.MAX_STAMPED], st[2 * self.MAX_STAMPED + 1]
+        if a and b and b >= a:
+            out["buffer_broadcast"] = {"start_ns": a, "end_ns": b, "us": (b - a) / 1e3}
+        return out
 
     def all_reduce_avg_(self, flat: torch.Tensor) -> None:
         """In-place average on the current stream (tensor inside the arena, or staged through it)."""
@@ -586,8 +628,8 @@ class P2PComm(CommBase):
         ready = torch.cuda.Event()
         ready.record(cur)
         self.stream.wait_event(ready)
-        native._call("b200_broadcast", self.arena.ctx(self.GRAD_CHANNEL), ctypes.c_size_t(base),
-                     ctypes.c_size_t(total), ctypes.c_int(0), ctypes.c_int(self.max_blocks),
+        native._call("b200_broadcast", self.arena.ctx(self.GRAD_CHANNEL, self._stamp_ptr(self.MAX_STAMPED)),
+                     ctypes.c_size_t(base), ctypes.c_size_t(total), ctypes.c_int(0), ctypes.c_int(self.max_blocks),
                      ctypes.c_void_p(self.stream.cuda_stream))
         self._ahead_event = torch.cuda.Event()
         self._ahead_event.record(self.stream)
@@ -607,7 +649,7 @@ class P2PComm(CommBase):
 
     # -- compressed wire format (comm hooks) -----------------------------------------------------------------
     def allreduce_wire16_(self, flat: torch.Tensor, wire: torch.dtype, stream: Optional[torch.cuda.Stream] = None,
-                          channel: Optional[int] = None) -> None:
+                          channel: Optional[int] = None, unit: Optional[int] = None) -> None:
         """In-place average of an fp32 arena tensor with bf16 / fp16 on the wire and fp32 accumulation."""
         off = self.arena.offset_of(flat)
         nbytes = flat.numel() * flat.element_size()
@@ -617,7 +659,8 @@ class P2PComm(CommBase):
         if nbytes // 2 > self._staging_bytes:
             raise RuntimeError("bucket too large for the staging region")
         stream = stream or torch.cuda.current_stream(self.device)
-        native._call("b200_allreduce_wire16", self.arena.ctx(self.MAIN_CHANNEL if channel is None else channel),
+        native._call("b200_allreduce_wire16", self.arena.ctx(self.MAIN_CHANNEL if channel is None else channel,
+                                                             self._stamp_ptr(unit)),
                      ctypes.c_size_t(off), ctypes.c_size_t(nbytes), ctypes.c_int(1 if wire == torch.bfloat16 else 2),
                      ctypes.c_float(1.0 / self.divisor), ctypes.c_size_t(self._staging),
                      ctypes.c_int(self.max_blocks), ctypes.c_void_p(stream.cuda_stream))

@@ -72,6 +72,14 @@ def format_ddp_stats(log: dict, samples: int, seconds: float) -> str:
         exposed = max(comm - overlap, 0.0)
         lines.append(f"[ddp] host-timed per iteration: forward {float(log.get('avg_forward_compute_time_ms') or 0):.3f} ms, "
                      f"backward {bwd:.3f} ms, communication {comm:.3f} ms of which {exposed:.3f} ms not overlapped")
+    dt = log.get("device_timing") or {}
+    if "step_us" in dt:
+        lines.append(f"[ddp] device-timed last step: {dt['step_us']:.1f} us = forward {dt.get('forward_us', 0):.1f} + backward "
+                     f"{dt.get('backward_us', 0):.1f} + tail; communication busy {dt.get('comm_busy_us', 0):.1f} us over a span of "
+                     f"{dt.get('comm_span_us', 0):.1f} us, exposed after backward {dt.get('exposed_comm_us', 0):.1f} us "
+                     f"({dt.get('exposed_comm_pct', 0):.1f} % of the step)")
+    for u in dt.get("units", []):
+        lines.append(f"[ddp]   launch unit {u['unit']}: {u['bytes']} B in {u['us']:.1f} us = {u['bus_gbs']:.0f} GB/s bus")
     cs = log.get("comm_stats") or {}
     if "avg_bucket_allreduce_us" in cs:
         lines.append(f"[ddp] device-timed bucket all-reduce: {cs['avg_bucket_allreduce_us']:.1f} us average over "
@@ -116,6 +124,8 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
     model = DDP(model, device_ids=[device.index] if device.type == "cuda" else None,
                 broadcast_buffers=cfg.broadcast_buffers, bucket_cap_mb=cfg.bucket_cap_mb,
                 first_bucket_mb=cfg.first_bucket_mb, comm=cfg.comm, allreduce_algo=cfg.allreduce_algo)   # :39
+    if cfg.print_ddp_stats:
+        model.enable_device_timing()          # before the step is captured: the marks become graph nodes
     criterion = CrossEntropyLoss()                                          # dpp.py:40
     optimizer = build_optimizer(cfg, model.parameters())                    # dpp.py:41
 
@@ -158,6 +168,8 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
             break
     stats = {"steps": global_step, "loss_history": history, "graph_replays": step_fn.replays,
              "ddp": model._get_ddp_logging_data()}
+    if cfg.print_ddp_stats and device.type == "cuda":
+        stats["ddp"]["device_timing"] = model.device_timing()
     if cfg.print_ddp_stats and rank == 0:
         print(format_ddp_stats(stats["ddp"], seen * world_size, time.time() - t0), flush=True)
     del step_fn

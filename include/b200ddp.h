@@ -18,6 +18,12 @@
 extern "C" {
 #endif
 
+/* ---- programmatic dependent launch ------------------------------------------------------
+ * The kernels of the training step are launched with cudaLaunchAttributeProgrammaticStreamSerialization:
+ * a kernel's prologue may overlap the tail of its predecessor in the stream, and it executes
+ * griddepcontrol.wait before its first global-memory access.  Default on (env B200DDP_PDL=0 turns it off). */
+void b200_set_pdl(int enabled);
+
 /* ---- input pipeline --------------------------------------------------------------------
  * uint8 NHWC image batch -> fp32 NHWC, (x/255 - mean)/std: the ToTensor+Normalize transform
  * of REF:32, done on the device after a 4x smaller H2D copy. */
@@ -74,6 +80,20 @@ int b200_bn_bwd_apply(const float* dy, const float* out, const float* x, const f
                       const float* save_mean, const float* save_invstd, const float* sums, float* dx,
                       float* dres, float* dgamma, float* dbeta, int accumulate_param_grads,
                       float* zero_after, int zero_count, int M, int C, int relu, cudaStream_t stream);
+
+/* Cluster BatchNorm (one launch, one 8-CTA cluster, tensor register-resident, fixed-order reduction through
+ * distributed shared memory: bit-reproducible).  For M*C <= 131072 and C/4 dividing 512; otherwise returns
+ * cudaErrorNotSupported and the caller uses the streaming kernels above.  The forward computes exact two-pass
+ * statistics itself (no `sums` input): it is the variance-robust / deterministic alternative to statistics
+ * accumulated by the convolution epilogue. */
+int b200_bn_bwd_cluster(const float* dy, const float* out, const float* x, const float* gamma,
+                        const float* save_mean, const float* save_invstd, float* dx, float* dres, float* dgamma,
+                        float* dbeta, int accumulate_param_grads, float* zero_after, int zero_count, int M, int C,
+                        int relu, cudaStream_t stream);
+int b200_bn_fwd_cluster(const float* x, const float* gamma, const float* beta, const float* residual, float* out,
+                        float* running_mean, float* running_var, long long* num_batches_tracked, float* save_mean,
+                        float* save_invstd, float* zero_after, int zero_count, int M, int C, float momentum,
+                        float eps, int relu, cudaStream_t stream);
 
 /* reduce + apply in one launch (blocks meet on `tickets`, 2 zero-initialised words left at zero) */
 int b200_bn_bwd_fused(const float* dy, const float* out, const float* x, const float* gamma,
@@ -214,6 +234,9 @@ int b200_allreduce_wire16(const void* ctx, size_t offset, size_t nbytes, int wir
                           int max_blocks, cudaStream_t stream);
 int b200_broadcast(const void* ctx, size_t offset, size_t nbytes, int root, int max_blocks, cudaStream_t stream);
 int b200_barrier(const void* ctx, cudaStream_t stream);
+/* device-timed logger: write %globaltimer (ns) to *dst on `stream`; the collective kernels stamp their own start / end
+ * into the context's `stamps` pair when it is set */
+int b200_stamp(unsigned long long* dst, cudaStream_t stream);
 /* set-up helpers (these DO allocate / map memory; call once, outside any capture) */
 int b200_arena_alloc(size_t bytes, void** out);
 int b200_arena_free(void* p);

@@ -73,9 +73,21 @@ def test_conv_fused_bn_stats(nat):
     assert torch.allclose(stats[128:], (y * y).sum(dim=(0, 2, 3)), rtol=1e-4, atol=1e-3)
 
 
-@pytest.mark.parametrize("n,c,h", [(32, 64, 16), (32, 128, 4), (32, 512, 1), (10, 256, 2), (4, 2048, 7)])
+@pytest.fixture(params=["stream", "cluster"])
+def bn_mode(request, nat):
+    """stream: statistics from float-atomic accumulators + two-kernel backward; cluster: the one-launch deterministic
+    cluster kernels (exact two-pass forward statistics, fused backward) wherever the shape qualifies."""
+    old = (nat.bn_stats_mode(), nat._BN_CLUSTER_BWD)
+    nat.set_bn_stats_mode("exact" if request.param == "cluster" else "fused")
+    nat._BN_CLUSTER_BWD = request.param == "cluster"
+    yield request.param
+    nat.set_bn_stats_mode(old[0])
+    nat._BN_CLUSTER_BWD = old[1]
+
+
+@pytest.mark.parametrize("n,c,h", [(32, 64, 16), (32, 64, 8), (32, 128, 4), (32, 512, 1), (10, 256, 2), (4, 2048, 7)])
 @pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
-def test_batchnorm_fused(nat, n, c, h, relu, res):
+def test_batchnorm_fused(nat, bn_mode, n, c, h, relu, res):
     torch.manual_seed(1)
     x = _cl(torch.randn(n, c, h, h, device="cuda") * 2 + 0.5).requires_grad_(True)
     r = _cl(torch.randn(n, c, h, h, device="cuda")).requires_grad_(True) if res else None
@@ -112,6 +124,43 @@ def test_batchnorm_fused(nat, n, c, h, relu, res):
     # self-cleaning accumulators: a second round gives the same answer
     out2 = nat.batch_norm_act(x, g, b, rm, rv, nbt, r, relu, True, 0.1, 1e-5, ws, False)
     assert _rel(out2, ref) < 1e-4
+
+
+def test_batchnorm_cluster_kernels_are_exact_for_large_means_and_reproducible(nat):
+    """|mean| >> std: E[x^2] - E[x]^2 in fp32 loses the variance; the cluster forward centres the data first.  Run
+    twice: the fixed-order cluster reductions give the same bits."""
+    old = (nat.bn_stats_mode(), nat._BN_CLUSTER_BWD)
+    nat.set_bn_stats_mode("exact")
+    nat._BN_CLUSTER_BWD = True
+    try:
+        torch.manual_seed(3)
+        n, c, h = 32, 128, 4
+        x = _cl(torch.randn(n, c, h, h, device="cuda") * 0.05 + 50.0).requires_grad_(True)
+        g = (torch.rand(c, device="cuda") + 0.5).requires_grad_(True)
+        b = torch.randn(c, device="cuda").requires_grad_(True)
+        dout = _cl(torch.randn(n, c, h, h, device="cuda"))
+        runs = []
+        for _ in range(2):
+            rm, rv = torch.zeros(c, device="cuda"), torch.ones(c, device="cuda")
+            nbt = torch.zeros((), dtype=torch.int64, device="cuda")
+            ws = nat.BNWorkspace(c, x.device)
+            out = nat.batch_norm_act(x, g, b, rm, rv, nbt, None, True, True, 0.1, 1e-5, ws, False)
+            grads = torch.autograd.grad(out, (x, g, b), dout)
+            runs.append((out.detach().clone(), rm.clone(), rv.clone()) + tuple(t.clone() for t in grads))
+        for a, bb in zip(runs[0], runs[1]):
+            assert torch.equal(a, bb)
+        xd = x.detach().double().requires_grad_(True)
+        gd, bd = g.detach().double().requires_grad_(True), b.detach().double().requires_grad_(True)
+        ref = F.relu(F.batch_norm(xd, None, None, gd, bd, True, 0.1, 1e-5))
+        assert _rel(runs[0][0], ref) < 1e-3
+        var = x.detach().double().var(dim=(0, 2, 3), unbiased=True)
+        assert torch.allclose(runs[0][2].double(), 0.9 + 0.1 * var, rtol=1e-3, atol=1e-7)
+        rgrads = torch.autograd.grad(ref, (xd, gd, bd), dout.double())
+        for a, bref in zip(runs[0][3:], rgrads):
+            assert _rel(a, bref) < 2e-3
+    finally:
+        nat.set_bn_stats_mode(old[0])
+        nat._BN_CLUSTER_BWD = old[1]
 
 
 def test_maxpool_matches_aten_including_ties(nat):
