@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(32) barrier_kernel(const CommCtx c) { block_ba
 // vectors [b*chunk, (b+1)*chunk) on EVERY rank, so block b's flag from peer p covers exactly the data block b reads.
 // Parity = epoch & 1 of this (channel, block): two pushes in a row alternate slots; if another collective ran on
 // the block in between, that collective's barrier already proves the peers are done with the previous push.
-constexpr int kPushVecPerThread = 4;
+constexpr int kPushVecPerThread = 1;      // small messages: spread the (N-1) remote stores per vector over many threads / blocks
 template <typename T>
 __global__ void __launch_bounds__(512) allreduce_push_kernel(const CommCtx c, size_t offset, size_t nvec, float scale,
                                                              size_t stage_off) {

@@ -47,6 +47,44 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   return v;
 }
 
+// Spin until *flag >= epoch (wrap-safe signed difference) or `timeout_ns` of wall time (%globaltimer) has passed.
+__device__ __forceinline__ bool wait_flag_ns(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
+  if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  unsigned spins = 0;
+  while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+    if ((++spins & 63u) == 0) {
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > timeout_ns) return false;
+    }
+  }
+  return true;
+}
+
+// NVLink multicast (NVLS) vector accesses: ld_reduce returns the SUM over all replicas (added in the switch, fp32
+// accumulation), st writes every replica.
+__device__ __forceinline__ uint4 multimem_ld_reduce_f32x4(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(void* p, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* p, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+               ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // ---- programmatic dependent launch (PDL) --------------------------------------------------------------------
 // The training step is a chain of ~140 short kernels; between two dependent kernels the GPU otherwise idles for the
 // launch latency plus the next kernel's prologue (barrier init, TMEM allocation, descriptor prefetch).  Kernels

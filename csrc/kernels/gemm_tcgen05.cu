@@ -107,6 +107,29 @@ struct PeerReduce {
   int pad;
 };
 
+// GEMM + in-switch all-reduce in ONE persistent kernel (the NVLS form of the fusion above; bf16 or fp32 output
+// that lives at the same offset of every rank's multicast-bound arena, e.g. a gradient-bucket slot):
+//   phase A  every rank computes its partial of every 256 x BN tile into ITS copy of the output and, per 128-row half
+//            tile, releases a flag on the half tile's owner rank (half % world);
+//   phase B  when a CTA has run out of tiles, ALL its warps turn to the half tiles this rank owns (32-row chunks,
+//            round-robin over the grid): wait for the world flags of the half tile, multimem.ld_reduce the chunk
+//            through the multicast mapping (the switch adds the ranks' partials, fp32 accumulate), scale by 1/world,
+//            multimem.st the result into every rank's copy, then release a "final" flag on every rank;
+//   phase C  every CTA waits for the final flags of its share of ALL half tiles, so kernel completion means this
+//            rank's copy is complete.  The last CTA to leave advances the launch epoch.
+// One writer per element and one fixed reduction order in the switch: replicas end bit-identical.  No staging, no
+// separate all-reduce launch, no entry barrier; early tiles are reduced while late tiles are still being computed.
+struct NvlsReduce {
+  unsigned char* mc_out;     // multicast mapping of the output matrix (element (r, c) at (r * ldo + c) * esize)
+  uint32_t* flags[8];        // each rank's flag object as mapped here: [half tile][8] partial-in-place epochs,
+                             // followed at word offset `final_off` by [half tile] final epochs
+  uint32_t* epoch;           // local: [0] launch epoch, [1] CTA exit ticket
+  unsigned long long timeout_ns;
+  int rank, world;
+  float scale;
+  int final_off;
+};
+
 struct Args {
   const void* a;
   const void* b;
@@ -135,6 +158,7 @@ struct Args {
   //   ((f_r0 + f_rstep * r) * f_S + (f_s0 + f_sstep * s)); filter_rs = R*S of the original filter
   int f_r0, f_rstep, f_s0, f_sstep, f_S, filter_rs;
   PeerReduce peer;             // world > 1: fused all-reduce epilogue (needs splits == 1, row-major out)
+  NvlsReduce nvls;             // world > 1: NVLS all-reduce fused into the persistent 2-CTA kernel
   // causal attention structure (batched calls): 1 = output tile is entirely above the diagonal -> skip it
   // (S = QK^T, dP = dO V^T); 2 = reduction index is the key, only keys <= query row matter (P V, dS K);
   // 3 = reduction index is the query, only queries >= key row matter (P^T dO, dS^T Q)
@@ -1072,6 +1096,93 @@ gemm2_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __gr
 //   tmem_empty[2]    : epilogue -> MMA, lives in the LEADER, 4 warps x 2 CTAs arrive (peer arrives remotely)
 // -----------------------------------------------------------------------------------------------------
 
+
+// Phases B and C of the NVLS-fused GEMM (see NvlsReduce): executed by every thread of every CTA of the persistent
+// kernel once the CTA has no tiles left.
+template <int BN>
+__device__ __forceinline__ void nvls_reduce_phases(const Args& a, int tiles_n, int num_tiles, uint32_t epoch) {
+  const NvlsReduce& nv = a.nvls;
+  __shared__ int nv_ok_s;
+  constexpr int CH = 32, QN = 128 / CH, U = 4;             // rows per work item, items per half tile, vectors in flight
+  const int t = threadIdx.x, nthr = blockDim.x;
+  const int halves = num_tiles * 2;
+  const int esize = a.out_bf16 ? 2 : 4;
+  const int owned = nv.rank < halves ? (halves - nv.rank + nv.world - 1) / nv.world : 0;
+  const unsigned long long limit = nv.timeout_ns ? nv.timeout_ns : 600ull * 1000ull * 1000ull * 1000ull;
+  for (int it = blockIdx.x; it < owned * QN; it += gridDim.x) {
+    const int h = nv.rank + (it / QN) * nv.world, q = it % QN;
+    if (t == 0) nv_ok_s = 1;
+    __syncthreads();
+    if (t < nv.world && !wait_flag_ns(nv.flags[nv.rank] + (size_t)h * 8 + t, epoch, limit)) {
+      nv_ok_s = 0;
+      if (a.error) atomicExch(a.error, 0xDEAD1000u | (unsigned)t);
+    }
+    __syncthreads();
+    const bool ok = nv_ok_s != 0;
+    const int tile = h >> 1;
+    const int m0 = (tile / tiles_n) * 2 * BM + (h & 1) * BM + q * CH, n0 = (tile % tiles_n) * BN;
+    const int vpr = min(BN, a.N - n0) * esize / 16;          // 16-byte vectors per row of this tile
+    const int total = CH * vpr;
+    for (int base = t; base < total; base += nthr * U) {
+      uint4 v[U];
+      size_t off[U];
+      bool live[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = base + u * nthr;
+        const int r = i / vpr, c = i - r * vpr;
+        live[u] = i < total && m0 + r < a.M;
+        off[u] = ((size_t)(m0 + r) * a.ldo + n0) * esize + (size_t)c * 16;
+        if (live[u] && ok) v[u] = a.out_bf16 ? multimem_ld_reduce_bf16x8(nv.mc_out + off[u]) : multimem_ld_reduce_f32x4(nv.mc_out + off[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!live[u]) continue;
+        if (!ok) {          // a peer never delivered: mark the local result instead of passing a partial sum off as final
+          *reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(a.out) + off[u]) =
+              make_uint4(0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u, 0x7fc07fc0u);
+          continue;
+        }
+        uint4 r4;
+        if (a.out_bf16) {
+          const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          uint32_t o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(w[j] << 16) * nv.scale,
+                                                            __uint_as_float(w[j] & 0xffff0000u) * nv.scale);
+            o[j] = *reinterpret_cast<const uint32_t*>(&hh);
+          }
+          r4 = make_uint4(o[0], o[1], o[2], o[3]);
+          multimem_st_bf16x8(nv.mc_out + off[u], r4);
+        } else {
+          r4 = make_uint4(__float_as_uint(__uint_as_float(v[u].x) * nv.scale), __float_as_uint(__uint_as_float(v[u].y) * nv.scale),
+                          __float_as_uint(__uint_as_float(v[u].z) * nv.scale), __float_as_uint(__uint_as_float(v[u].w) * nv.scale));
+          multimem_st_f32x4(nv.mc_out + off[u], r4);
+        }
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t < nv.world) st_release_sys(nv.flags[t] + nv.final_off + (size_t)h * QN + q, epoch);     // "chunk final" on every rank
+  }
+  // phase C: this rank's copy is complete when every chunk of every half tile has been finalised by its owner
+  bool all = true;
+  for (int c = blockIdx.x + t * gridDim.x; c < halves * QN; c += gridDim.x * nthr)
+    if (!wait_flag_ns(nv.flags[nv.rank] + nv.final_off + c, epoch, limit)) all = false;
+  if (!all && a.error) atomicExch(a.error, 0xDEAD2000u);
+  __syncthreads();
+  if (t == 0) {
+    __threadfence();
+    const unsigned k = atomicAdd(nv.epoch + 1, 1u);
+    if (k == gridDim.x - 1) {            // last CTA out: every CTA has read the epoch, nobody needs the old value
+      nv.epoch[1] = 0u;
+      __threadfence();
+      nv.epoch[0] = epoch;
+    }
+  }
+}
+
 template <int AK, int BK_, int BN, bool BF16, int ST>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T2P_THREADS, 1)
 gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
@@ -1092,6 +1203,7 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
   const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
   const int num_kb = (a.Kd + KELEMS - 1) / KELEMS;
   const uint32_t smem_a = (smem_u32(smem) + 1023u) & ~1023u, smem_b = smem_a + ST * A_STAGE;
+  const uint32_t nv_epoch = a.nvls.world > 1 ? *reinterpret_cast<volatile uint32_t*>(a.nvls.epoch) + 1u : 0u;
 
   if (t == 96) {
     tma_prefetch_desc(&map_a);
@@ -1240,12 +1352,22 @@ gemm2p_kernel(const Args a, const __grid_constant__ CUtensorMap map_a, const __g
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(buf ? empty_leader1 : empty_leader0);
+      if (a.nvls.world > 1) {
+        // NVLS fusion, phase A: this CTA's 128 rows of the tile are in this rank's copy of the output -- tell the owner
+        __threadfence_system();
+        asm volatile("bar.sync 2, 256;" ::: "memory");       // the 8 epilogue warps
+        if (warp == 4 && lane == 0) {
+          const int h = tile * 2 + (int)cta;
+          st_release_sys(a.nvls.flags[h % a.nvls.world] + (size_t)h * 8 + a.nvls.rank, nv_epoch);
+        }
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();
   if (warp == 2) tmem_dealloc2(tmem_d, TMEM_COLS);
+  if (a.nvls.world > 1) nvls_reduce_phases<BN>(a, tiles_n, num_tiles, nv_epoch);
 }
 
 // wt[c][R-1-r][S-1-s][k] = w[k][r][s][c]: the filter of the convolution that computes dX from dY (stride 1).
@@ -1432,6 +1554,7 @@ static int try_2cta(const Args& a, cudaStream_t st) {
   if constexpr (a_ok && b_ok) {
     if (a.epi != 0 && (g_use_2cta < 2 || !a.out_bf16 || a.N % 16 || a.ldo % 8 || a.accumulate)) return -1;
     if (!g_use_2cta || !g_use_tma || a.batch > 1 || a.transpose_out || a.stats != nullptr || a.peer.world > 1) return -1;
+    if (a.nvls.world > 1 && (g_use_2cta < 2 || a.epi != 0 || a.accumulate || a.bias != nullptr)) return -1;
     if (a.M < 512 || a.N < 128) return -1;
     // 256 x 256 or 256 x 128 cluster tiles: whichever needs less time on 74 clusters (rounds x tile width);
     // ties go to the wider tile (half the A traffic per flop)
@@ -1796,3 +1919,43 @@ B200_API int b200_gemm_tc_peer(const void* A, const void* B, const void* bias, i
 }
 
 B200_API int b200_peer_reduce_bytes(void) { return (int)sizeof(PeerReduce); }
+
+// GEMM whose epilogue is the NVLS all-reduce (average) of its output: see NvlsReduce.  Same operand conventions as
+// b200_gemm_tc_ex (mode 0/1/2, desc = {lda, ldb, ldo}); flags bit 0 = bf16 operands, bit 1 = bf16 output.  `nvls` is a
+// host copy of NvlsReduce.  The output must live at the same offset of every rank's multicast-bound arena.
+// Flag object per rank: b200_gemm_tc_nvls_flag_words(M, N) 32-bit words, zero-initialised once.
+// Returns cudaErrorNotSupported (801) when the shape does not run on the persistent 2-CTA kernel (then call the
+// plain GEMM followed by an all-reduce).
+B200_API int b200_nvls_reduce_bytes(void) { return (int)sizeof(NvlsReduce); }
+B200_API int b200_gemm_tc_nvls_flag_words(int M, int N) {
+  const int halves = 2 * ceil_div(M, 2 * BM) * ceil_div(N, 128);        // upper bound over both tile widths
+  return halves * 8 + halves * 4;
+}
+B200_API int b200_gemm_tc_nvls_final_off(int M, int N) { return 2 * ceil_div(M, 2 * BM) * ceil_div(N, 128) * 8; }
+
+B200_API int b200_gemm_tc_nvls(const void* A, const void* B, void* out_local, int M, int N, int K, int mode, int flags,
+                               const long long* desc, const void* nvls, unsigned* error, cudaStream_t stream) {
+  const bool bf16 = flags & 1;
+  const int vec = bf16 ? 8 : 4;
+  if (!ptr16(A) || !ptr16(B) || !ptr16(out_local) || M <= 0 || N <= 0 || K <= 0) return static_cast<int>(cudaErrorInvalidValue);
+  Args a{};
+  a.nvls = *static_cast<const NvlsReduce*>(nvls);
+  if (a.nvls.world < 2 || a.nvls.world > 8 || a.nvls.mc_out == nullptr) return static_cast<int>(cudaErrorInvalidValue);
+  a.a = A; a.b = B; a.out = static_cast<float*>(out_local);
+  a.M = M; a.N = N; a.Kd = K;
+  a.lda = desc[0]; a.ldb = desc[1]; a.ldo = desc[2];
+  a.batch = 1; a.inner = 1;
+  a.out_bf16 = (flags >> 1) & 1;
+  a.error = error;
+  const int ovec = a.out_bf16 ? 8 : 4;
+  if (a.lda % vec || a.ldb % vec || a.ldo % ovec || N % ovec) return static_cast<int>(cudaErrorInvalidValue);
+  int rc = -1;
+  if (bf16) {
+    if (mode == 0) rc = try_2cta<DENSE_K, DENSE_K, true>(a, stream);
+    else if (mode == 1) rc = try_2cta<DENSE_K, DENSE_MN, true>(a, stream);
+    else if (mode == 2) rc = try_2cta<DENSE_MN, DENSE_MN, true>(a, stream);
+  } else if (mode == 0) {
+    rc = try_2cta<DENSE_K, DENSE_K, false>(a, stream);
+  }
+  return rc < 0 ? static_cast<int>(cudaErrorNotSupported) : rc;
+}

@@ -18,6 +18,12 @@ SURVEY §3.4), identical on every rank -- runs eagerly the first time it is seen
 convolution tuner needs one eager pass per new geometry) and is captured the second time, up
 to ``max_graphs`` graphs (``B200DDP_MAX_GRAPHS``, default 2).
 
+Optimizer in backward: with this framework's fused SGD (one param group) and the P2P / single-process data plane,
+the update of a gradient bucket's parameters is enqueued right behind that bucket's reduction on the communication
+stream (``comm.after_reduce``), so it runs under the rest of the backward pass; only the few KB of the last launch
+unit are updated after backward ends.  Same arithmetic as ``optimizer.step()``, earlier in time (nothing in the
+backward pass reads a parameter after its gradient is complete).  ``overlap_optimizer=False`` switches it off.
+
 After every step the DDP wrapper's health word (pinned host memory, written by a collective
 kernel whose peer never arrived) is read; a set word raises on this rank.
 """
@@ -31,7 +37,7 @@ import torch.nn as nn
 
 class TrainStep:
     def __init__(self, model: nn.Module, criterion: Callable, optimizer: torch.optim.Optimizer,
-                 cuda_graph: bool = True, warmup_steps: int = 3) -> None:
+                 cuda_graph: bool = True, warmup_steps: int = 3, overlap_optimizer: bool = True) -> None:
         self.model = model
         self.criterion = criterion
         self.optimizer = optimizer
@@ -47,7 +53,36 @@ class TrainStep:
         import os
 
         self.max_graphs = int(os.environ.get("B200DDP_MAX_GRAPHS", "2"))
+        self._updated = set()          # ids of the parameters already updated by per-bucket optimizer launches
+        self._overlap_opt = False
+        if (overlap_optimizer and os.environ.get("B200DDP_OVERLAP_OPT", "1") != "0" and self._ddp is not None
+                and dev.type == "cuda" and getattr(optimizer, "supports_subset_steps", lambda: False)()
+                and getattr(self._ddp.comm, "name", "") in ("p2p", "none")):
+            import weakref
+
+            me = weakref.ref(self)
+            self._opt_ids = {id(p) for g in optimizer.param_groups for p in g["params"]}
+            self._ddp.comm.after_reduce = lambda index: me() is not None and me()._after_reduce(index)
+            self._overlap_opt = True
         self._nvtx = dev.type == "cuda" and os.environ.get("B200DDP_NVTX", "0") != "0"
+
+    def _after_reduce(self, index: int) -> None:
+        """Runs on the stream that carries launch unit ``index``'s reduction, right behind it."""
+        ddp = self._ddp
+        if ddp._join_enabled or not ddp.training:
+            return                   # uneven-input shadow iterations / evaluation: the ordinary step() decides
+        ps = [ddp._params[i] for i in ddp.reducer.bucket_params()[index]]
+        ps = [p for p in ps if id(p) in self._opt_ids and p.grad is not None]
+        if ps:
+            self.optimizer.step_subset(index, ps)
+            self._updated.update(id(p) for p in ps)
+
+    def _optimizer_step(self) -> None:
+        if self._overlap_opt and self._updated:
+            done, self._updated = self._updated, set()
+            self.optimizer.step(skip=done)          # whatever no bucket launch covered (nothing in steady state)
+        else:
+            self.optimizer.step()
 
     def _forward_loss(self, data, target):
         inner = getattr(self.model, "module", self.model)
@@ -58,6 +93,7 @@ class TrainStep:
     # -- eager ---------------------------------------------------------------------------
     def _eager(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         nvtx = self._nvtx
+        self._updated = set()
         self.optimizer.zero_grad()
         if nvtx:
             torch.cuda.nvtx.range_push("b200ddp.forward")
@@ -69,7 +105,7 @@ class TrainStep:
         if nvtx:
             torch.cuda.nvtx.range_pop()
             torch.cuda.nvtx.range_push("b200ddp.optimizer")
-        self.optimizer.step()
+        self._optimizer_step()
         if self._ddp is not None:
             self._ddp._mark(self._ddp.STEP_END)
         if nvtx:
@@ -88,6 +124,7 @@ class TrainStep:
     def _capture(self, data: torch.Tensor, target: torch.Tensor) -> dict:
         static_x = data.clone(memory_format=torch.preserve_format)
         static_y = target.clone()
+        self._updated = set()
         self.optimizer.zero_grad(set_to_none=True)
         from .ops import native
 
@@ -112,7 +149,7 @@ class TrainStep:
             with torch.cuda.graph(graph, stream=cap_stream, capture_error_mode="thread_local"):
                 loss = self._forward_loss(static_x, static_y)
                 loss.backward()
-                self.optimizer.step()
+                self._optimizer_step()
                 if self._ddp is not None:
                     self._ddp._mark(self._ddp.STEP_END)
                 # drop the autograd graph now: it keeps the capture-stream accumulator nodes alive

@@ -35,6 +35,16 @@ class _Done:
         return None
 
 
+class _EventHandle:
+    """Completion of work issued on another CUDA stream: ``wait()`` orders the current stream after it."""
+
+    def __init__(self, event) -> None:
+        self.event = event
+
+    def wait(self) -> None:
+        torch.cuda.current_stream().wait_event(self.event)
+
+
 class _WorkHandle:
     def __init__(self, work, post: Optional[Callable[[], None]] = None) -> None:
         self._work = work
@@ -59,6 +69,11 @@ class CommBase:
         # ``DistributedDataParallel.join(divide_by_initial_world_size=False)`` where it is the number of ranks
         # that still have data this iteration
         self.divisor = self.world_size
+        # Optional ``fn(unit_index)`` run right after a launch unit's reduction has been enqueued, ON THE STREAM THAT
+        # CARRIES THE REDUCTION: the training step uses it to apply the optimizer update of that unit's parameters
+        # while the backward pass is still running (engine.TrainStep, "optimizer in backward").
+        self.after_reduce: Optional[Callable[[int], None]] = None
+        self._side_stream = None
 
     # bucket memory -------------------------------------------------------------------
     def allocate(self, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
@@ -105,11 +120,26 @@ class NoComm(CommBase):
 
     def launch(self, index, flat, is_last):
         self.launches += 1
-        if flat.is_cuda:
-            from ..ops import native
+        if not flat.is_cuda:
+            return _Done()
+        from ..ops import native
 
+        if self.after_reduce is None:
             native.join_side_streams(flat.device)
-        return _Done()
+            return _Done()
+        # single process: nothing to reduce, but the unit's optimizer update can already run next to the backward pass
+        if self._side_stream is None:
+            self._side_stream = torch.cuda.Stream(device=flat.device)
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(flat.device))
+        self._side_stream.wait_event(ready)
+        for ev in native.side_stream_events(flat.device):
+            self._side_stream.wait_event(ev)
+        with torch.cuda.stream(self._side_stream):
+            self.after_reduce(index)
+        done = torch.cuda.Event()
+        done.record(self._side_stream)
+        return _EventHandle(done)
 
     def broadcast_(self, flat, src=0):
         return None

@@ -25,7 +25,7 @@ import torch
 import torch.distributed as dist
 
 from ..ops import native
-from .comm import CommBase, _Done
+from .comm import CommBase, _Done, _EventHandle
 
 _DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1}
 HEADER_BYTES = 64 << 10          # signal pad + epoch counters + error word
@@ -277,14 +277,6 @@ class SymmetricArena:
             self._opened = []
 
 
-class _EventHandle:
-    def __init__(self, event: torch.cuda.Event) -> None:
-        self.event = event
-
-    def wait(self) -> None:
-        torch.cuda.current_stream().wait_event(self.event)
-
-
 class P2PComm(CommBase):
     """Gradient buckets reduced by our NVLink kernels on a high-priority side stream."""
 
@@ -299,8 +291,16 @@ class P2PComm(CommBase):
         self.max_blocks = int(max_blocks or os.environ.get("B200DDP_COMM_BLOCKS", 32))
         self.last_blocks = int(os.environ.get("B200DDP_COMM_BLOCKS_LAST", self.max_blocks))
         self.nvls_blocks = int(os.environ.get("B200DDP_NVLS_BLOCKS", 24))     # the switch reduces: few SMs suffice
-        self.nvls_min_world = int(os.environ.get("B200DDP_NVLS_MIN_WORLD", 4))
-        self.nvls_min_bytes = int(os.environ.get("B200DDP_NVLS_MIN_BYTES", 1 << 20))
+        # algorithm boundaries, from the graph-timed sweeps on B200 (profiles/allreduce_sweep_n{2,4,8}.json):
+        #   push (one flag exchange)  wins up to 256 KB on 2 ranks, 16 KB on 4, 8 KB on 8 (its (N-1) stores per vector grow
+        #                             with the rank count);
+        #   NVLS (in-switch)          wins from 256 KB on 8 ranks, only from 128 MB on 4, never on 2;
+        #   two-shot                  everything in between.
+        ws = self.world_size
+        self.push_auto_max = int(os.environ.get("B200DDP_PUSH_MAX_BYTES",
+                                                (256 << 10) if ws <= 2 else (16 << 10) if ws <= 4 else (8 << 10)))
+        self.nvls_min_world = int(os.environ.get("B200DDP_NVLS_MIN_WORLD", 3))
+        self.nvls_min_bytes = int(os.environ.get("B200DDP_NVLS_MIN_BYTES", (128 << 20) if ws <= 5 else (256 << 10)))
         self.oneshot_max = int(os.environ.get("B200DDP_ONESHOT_MAX_BYTES", 256 << 10))
         self._arena_bytes = arena_bytes
         self.arena: Optional[SymmetricArena] = None
@@ -373,7 +373,7 @@ class P2PComm(CommBase):
         if self.algo == "twoshot":
             return 2
         if self.algo == "auto":
-            if nbytes <= min(self.oneshot_max, self.push_max):
+            if nbytes <= min(self.push_auto_max, self.push_max):
                 return 4
             # NVLS pays off where the switch saves link traffic: from 4 ranks up (on 2 ranks the two-shot kernel moves
             # S/2 per direction and is faster: 32 MB 67 us vs 106 us measured)
@@ -445,6 +445,9 @@ class P2PComm(CommBase):
         if 0 <= index < self.MAX_STAMPED:
             self._stamp_bytes[index] = nbytes
         self.algo_counts[name] = self.algo_counts.get(name, 0) + 1
+        if self.after_reduce is not None and expect is None:
+            with torch.cuda.stream(self.stream):
+                self.after_reduce(index)            # e.g. the optimizer update of this unit, behind its reduction
         done = torch.cuda.Event(enable_timing=t0 is not None)
         done.record(self.stream)
         if t0 is not None:
@@ -781,6 +784,58 @@ class FusedGradReduce:
         if self._epoch is None:
             self._epoch = arena.alloc(256)
             arena.memory[self._epoch:self._epoch + 256].zero_()
+
+    # -- NVLS form: persistent 2-CTA GEMM whose tail reduces the output through the switch ------------------------
+    def _nvls_reserve(self, n_out: int, k_in: int):
+        lib = _lib()
+        arena = self.comm.arena
+        words = int(lib.b200_gemm_tc_nvls_flag_words(ctypes.c_int(n_out), ctypes.c_int(k_in)))
+        st = getattr(self, "_nvls_state", None)
+        if st is None or st["words"] < words:
+            off = arena.alloc(words * 4)
+            arena.memory[off:off + words * 4].zero_()
+            ep = st["epoch"] if st is not None else None
+            if ep is None:
+                ep = torch.zeros(4, dtype=torch.int32, device=self.comm.device)
+            st = self._nvls_state = {"off": off, "words": words, "epoch": ep}
+            torch.cuda.synchronize(self.comm.device)
+            dist.barrier(group=self.comm.group)          # every rank's flag object is zeroed before anyone signals
+        return st
+
+    def wgrad_nvls(self, dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor) -> bool:
+        """``out = mean_r(dy_r^T @ x_r)`` by ONE kernel: the persistent tcgen05 GEMM writes each rank's partial tiles
+        into its copy of ``out`` and its tail phase all-reduces them in the NVLink switch (multimem.ld_reduce / st),
+        tile by tile as they complete.  Returns False when the shape does not run on that kernel (the caller then runs
+        GEMM + all-reduce).  The first call for a larger flag object is a collective (it barriers once)."""
+        arena = self.comm.arena
+        off = arena.offset_of(out) if arena is not None else None
+        if off is None or not arena.multicast or not out.is_contiguous():
+            return False
+        m_tok, n_out = dy.shape
+        k_in = x.shape[1]
+        lib = _lib()
+        st = self._nvls_reserve(n_out, k_in)
+        final_off = int(lib.b200_gemm_tc_nvls_final_off(ctypes.c_int(n_out), ctypes.c_int(k_in)))
+        world, rank = self.comm.world_size, self.comm.rank
+        pad = [0] * (8 - world)
+        raw = struct.pack("<Q8QQQiifi", arena.multicast + off, *[b + st["off"] for b in arena.peer_base], *pad,
+                          st["epoch"].data_ptr(), arena.timeout_ns, rank, world, 1.0 / self.comm.divisor, final_off)
+        assert len(raw) == lib.b200_nvls_reduce_bytes(), (len(raw), lib.b200_nvls_reduce_bytes())
+        nv = ctypes.create_string_buffer(raw, len(raw))
+        flags = int(dy.dtype == torch.bfloat16) | (int(out.dtype == torch.bfloat16) << 1)
+        desc = (ctypes.c_longlong * 3)(n_out, k_in, k_in)
+        err = native.scratch(dy.device).error
+        rc = lib.b200_gemm_tc_nvls(ctypes.c_void_p(dy.data_ptr()), ctypes.c_void_p(x.data_ptr()),
+                                   ctypes.c_void_p(out.data_ptr()), ctypes.c_int(n_out), ctypes.c_int(k_in),
+                                   ctypes.c_int(m_tok), ctypes.c_int(2), ctypes.c_int(flags), desc, nv,
+                                   ctypes.c_void_p(err.data_ptr()),
+                                   ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc == 801:
+            return False
+        if rc != 0:
+            raise RuntimeError(f"b200_gemm_tc_nvls failed: CUDA error {rc}")
+        native._launches += 1
+        return True
 
     def wgrad(self, dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor) -> None:
         """out[N_out, K_in] (arena resident, same offset on every rank) = mean_r(dy_r^T @ x_r)."""

@@ -199,6 +199,52 @@ def fused_wgrad_worker(rank, ws, port, out_dir):
             e2.record()
             torch.cuda.synchronize()
             rec["times"][(str(dtype), tok, n_out, k_in)] = (e0.elapsed_time(e1) / 5, e1.elapsed_time(e2) / 5)
+    # ---- NVLS form: persistent 2-CTA GEMM + in-switch reduction in one kernel (bf16, multicast arena) ----
+    rec["nvls"] = {"available": bool(comm.arena.multicast), "times": {}, "fails": []}
+    if comm.arena.multicast:
+        from distributeddataparallel_b200.ops import native_tf
+
+        for (tok, n_out, k_in) in [(4096, 1024, 1024), (8192, 4096, 1024), (8192, 1024, 4096), (8192, 3072, 1024)]:
+            dy = torch.randn(tok, n_out, generator=g).to(torch.bfloat16).to(dev)
+            x = torch.randn(tok, k_in, generator=g).to(torch.bfloat16).to(dev)
+            out = comm.allocate(n_out * k_in, torch.bfloat16, dev).view(n_out, k_in)
+            tmp = comm.allocate(n_out * k_in, torch.bfloat16, dev).view(n_out, k_in)
+            # reference with the same rounding points: per-rank product rounded to bf16, summed in fp32, scaled, rounded
+            part = (dy.float().t() @ x.float()).to(torch.bfloat16).float()
+            dist.all_reduce(part)
+            ref = (part / ws).to(torch.bfloat16)
+            ok_shape = True
+            for rep in range(3):
+                out.fill_(float("nan"))
+                torch.cuda.synchronize(); dist.barrier()
+                ok_shape = fused.wgrad_nvls(dy, x, out)
+                if not ok_shape:
+                    break
+            torch.cuda.synchronize()
+            if not ok_shape:
+                rec["nvls"]["fails"].append(("not eligible", tok, n_out, k_in))
+                continue
+            gathered = [torch.empty_like(out) for _ in range(ws)]
+            dist.all_gather(gathered, out)
+            same = all(torch.equal(gathered[0], t) for t in gathered)
+            err = float((out.float() - ref.float()).norm() / ref.float().norm())
+            if not (same and err < 1e-2 and bool(torch.isfinite(out).all())):
+                rec["ok"] = False
+                rec["nvls"]["fails"].append((tok, n_out, k_in, same, err))
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            torch.cuda.synchronize(); dist.barrier()
+            e0.record()
+            for _ in range(10):
+                fused.wgrad_nvls(dy, x, out)
+            e1.record()
+            for _ in range(10):
+                native_tf.gemm_ex(dy, x, tmp, 2, n_out, k_in, tok, n_out, k_in, k_in)
+                comm.all_reduce_avg_(tmp.view(-1))
+            e2.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / 10, e1.elapsed_time(e2) / 10], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            rec["nvls"]["times"][(tok, n_out, k_in)] = tuple(round(float(v), 4) for v in t)
     comm.check()
     rec["tc_error"] = native.tc_error_word(dev)
     torch.save(rec, os.path.join(out_dir, f"fused{rank}.pt"))

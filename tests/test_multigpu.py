@@ -42,7 +42,7 @@ def test_ddp_p2p_end_to_end(tmp_path):
         assert rec["rebuilt"] == [9_461_800, 26_494_976, 8_769_792]
         # the last bucket is streamed: its tail unit is the stem's 37 632-byte weight gradient (+ bn1), pushed
         assert len(rec["launch_units"]) > 3 and sum(rec["launch_units"]) == 44_726_568 and rec["launch_units"][-1] <= 65_536
-        assert rec["algo_counts"].get("push", 0) > 0
+        assert sum(rec["algo_counts"].values()) >= len(rec["launch_units"])
         assert rec["graphs"] == 2            # steady-state batch + ragged tail
     print("ddp:", {k: recs[0][k] for k in ("provider", "multicast", "algo_counts", "launch_units")})
 
@@ -53,7 +53,10 @@ def test_fused_wgrad_allreduce(tmp_path):
     for r in range(n):
         rec = torch.load(tmp_path / f"fused{r}.pt")
         assert rec["ok"] and rec["tc_error"] == 0, rec
-    print("fused vs unfused ms:", torch.load(tmp_path / "fused0.pt")["times"])
+    rec0 = torch.load(tmp_path / "fused0.pt")
+    print("fused vs unfused ms:", rec0["times"])
+    print("NVLS-fused GEMM vs GEMM + all-reduce (ms):", rec0["nvls"])
+    assert not rec0["nvls"]["fails"], rec0["nvls"]
 
 
 def test_builtin_comm_hooks_are_fused_on_the_p2p_plane(tmp_path):
