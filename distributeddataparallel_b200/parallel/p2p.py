@@ -290,6 +290,13 @@ class P2PComm(CommBase):
         self.algo = algo
         self.max_blocks = int(max_blocks or os.environ.get("B200DDP_COMM_BLOCKS", 32))
         self.last_blocks = int(os.environ.get("B200DDP_COMM_BLOCKS_LAST", self.max_blocks))
+        # Gradient buckets reduced UNDER the backward pass use few CTAs: the reductions are switch / link bound, not
+        # SM bound, and every CTA they hold slows the latency-bound backward kernels they share the chip with
+        # (8 GPUs, NVLS, dpp.py step: 32 CTAs 0.820 ms, 16 CTAs 0.797 ms, 8 CTAs 0.785 ms per step and the reductions
+        # themselves did not get slower; the SM-driven two-shot kernel needs 16: 2 GPUs 0.768 ms vs 0.775 with 32 and
+        # 0.830 with 8).  Stand-alone collectives (all_reduce_avg_, the sweep) keep `max_blocks`.
+        self.overlap_blocks = int(os.environ.get("B200DDP_COMM_BLOCKS_OVERLAP", 16))
+        self.nvls_overlap_blocks = int(os.environ.get("B200DDP_NVLS_BLOCKS_OVERLAP", 8))
         self.nvls_blocks = int(os.environ.get("B200DDP_NVLS_BLOCKS", 24))     # the switch reduces: few SMs suffice
         # algorithm boundaries, from the graph-timed sweeps on B200 (profiles/allreduce_sweep_n{2,4,8}.json):
         #   push (one flag exchange)  wins up to 256 KB on 2 ranks, 16 KB on 4, 8 KB on 8 (its (N-1) stores per vector grow
@@ -304,7 +311,7 @@ class P2PComm(CommBase):
         self.oneshot_max = int(os.environ.get("B200DDP_ONESHOT_MAX_BYTES", 256 << 10))
         self._arena_bytes = arena_bytes
         self.arena: Optional[SymmetricArena] = None
-        self.stream = torch.cuda.Stream(device=device, priority=-1)
+        self.stream = torch.cuda.Stream(device=device, priority=int(os.environ.get("B200DDP_COMM_PRIORITY", "-1")))
         self._staging: Optional[int] = None
         self._staging_bytes = 0
         self._push_stage: Dict[int, int] = {}      # channel -> arena offset of the push all-reduce staging object
@@ -439,8 +446,10 @@ class P2PComm(CommBase):
             self.allreduce_wire16_(flat, wire, stream=self.stream, channel=self.GRAD_CHANNEL, unit=index)
             name = "wire16"
         else:
-            algo = self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype,
-                                      blocks=self.last_blocks if is_last else None, unit=index)
+            algo = self._pick_algo(nbytes)
+            blocks = self.last_blocks if is_last else (self.nvls_overlap_blocks if algo == 3 else self.overlap_blocks)
+            self._allreduce_on(self.stream, self.GRAD_CHANNEL, off, nbytes, flat.dtype, blocks=blocks, algo=algo,
+                               unit=index)
             name = self.ALGO_NAMES[algo]
         if 0 <= index < self.MAX_STAMPED:
             self._stamp_bytes[index] = nbytes
