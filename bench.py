@@ -50,8 +50,11 @@ def parse():
     p.add_argument("--algo", default="auto")
     p.add_argument("--no-graph", action="store_true")
     p.add_argument("--no-native", action="store_true", help="ours: library ops instead of the sm_100a kernels")
-    p.add_argument("--model", default="simplecnn")
-    p.add_argument("--batch", type=int, default=BATCH)
+    p.add_argument("--model", default="simplecnn",
+                   help="simplecnn (headline, BASELINE config 2) | resnet50 (config 3) | gpt2-medium (config 4)")
+    p.add_argument("--batch", type=int, default=None, help="per-GPU batch (32; 8 sequences for gpt2)")
+    p.add_argument("--dtype", default=None, help="extra workloads: bf16 | tf32 (default: bf16 for gpt2, tf32 for resnet50)")
+    p.add_argument("--seq-len", type=int, default=1024)
     return p.parse_args()
 
 
@@ -457,10 +460,179 @@ def run_reference(args, rank, local_rank, world):
     })
 
 
+# =========================================================================================
+# extra workloads (BASELINE.json configs 3 and 4): ResNet-50 on ImageNet-shaped batches, GPT-2 medium
+# =========================================================================================
+def run_extra(args, rank, local_rank, world):
+    """``--model resnet50|gpt2-medium`` for either arm.  ours: this framework (DDP + TrainStep, native kernels);
+    reference: the stock stack the reference script is written against -- torchvision / HF transformers models under
+    ``torch.nn.parallel.DistributedDataParallel`` over NCCL, eager, cuDNN / cuBLAS / SDPA -- none of this repo's code.
+    Same JSON contract as the headline: device-timed K steps (max over ranks), clocks sampled inside the region, and an
+    end-to-end figure that includes the pinned host->device copy of every step's inputs and a loss read-back."""
+    import torch
+    import torch.distributed as dist
+
+    ClockSampler = load_clock_sampler()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    ours = args.impl == "ours"
+    is_gpt = args.model.startswith("gpt2")
+    B = args.batch or (8 if is_gpt else 32)
+    dtype = args.dtype or ("bf16" if is_gpt else "tf32")
+    K, W, T = args.steps, args.warmup, args.seq_len
+    if world > 1 and not dist.is_initialized():
+        if ours:
+            import distributeddataparallel_b200 as d
+
+            d.setup(rank, world, backend="nccl")
+        else:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    torch.manual_seed(0)
+    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    pool_n = 8
+    if is_gpt:
+        host = [torch.randint(0, 50257, (B, T + 1), dtype=torch.int64, generator=g).pin_memory() for _ in range(pool_n)]
+        h2d = B * (T + 1) * 8
+    else:
+        host = [(torch.randint(0, 256, (B, 224, 224, 3), dtype=torch.uint8, generator=g).pin_memory(),
+                 torch.randint(0, 1000, (B,), dtype=torch.int64, generator=g).pin_memory()) for _ in range(pool_n)]
+        h2d = B * 224 * 224 * 3 + B * 8
+    launches_fn = lambda: 0
+    if ours:
+        import distributeddataparallel_b200 as d
+        from distributeddataparallel_b200.ops import native
+
+        if is_gpt:
+            from distributeddataparallel_b200.models.gpt2 import build_gpt2
+
+            model = build_gpt2(args.model, T).to(dev, torch.bfloat16 if dtype == "bf16" else torch.float32)
+            crit = None
+        else:
+            model = d.resnet50(1000).to(dev)
+            crit = d.CrossEntropyLoss()
+        ddp = d.DDP(model, device_ids=[local_rank], comm=args.comm, allreduce_algo=args.algo)
+        opt = d.SGD(ddp.parameters(), lr=0.01)
+        step = d.TrainStep(ddp, crit, opt, cuda_graph=not args.no_graph)
+
+        def to_device(h):
+            if is_gpt:
+                t = h.to(dev, non_blocking=True)
+                return t[:, :-1].contiguous(), t[:, 1:].contiguous()
+            return d.ops.preprocess_u8(h[0].to(dev, non_blocking=True)), h[1].to(dev, non_blocking=True)
+
+        run = lambda x, y: step(x, y)
+        comm_name = ddp.comm.name
+        launches_fn = lambda: native.launch_count() + step.replays * native.launches_per_capture()
+        api = "pinned batch -> H2D -> TrainStep(DDP(model), loss, SGD) -> loss.item()"
+    else:
+        from torch.nn.parallel import DistributedDataParallel as StockDDP
+
+        if is_gpt:
+            from transformers import GPT2Config, GPT2LMHeadModel
+
+            cfg = GPT2Config(n_layer=24, n_head=16, n_embd=1024, n_positions=T, vocab_size=50257, attn_pdrop=0.0,
+                             embd_pdrop=0.0, resid_pdrop=0.0) if args.model == "gpt2-medium" else GPT2Config()
+            cfg._attn_implementation = "sdpa"
+            model = GPT2LMHeadModel(cfg).to(dev, torch.bfloat16 if dtype == "bf16" else torch.float32)
+        else:
+            import torchvision
+
+            model = torchvision.models.resnet50(weights=None).to(dev).to(memory_format=torch.channels_last)
+        net = StockDDP(model, device_ids=[local_rank]) if world > 1 else model
+        opt = torch.optim.SGD(model.parameters(), lr=0.01)
+
+        def to_device(h):
+            if is_gpt:
+                t = h.to(dev, non_blocking=True)
+                return t[:, :-1].contiguous(), t[:, 1:].contiguous()
+            x = h[0].to(dev, non_blocking=True).permute(0, 3, 1, 2).float().div_(255.0).sub_(0.5).div_(0.5)
+            return x.contiguous(memory_format=torch.channels_last), h[1].to(dev, non_blocking=True)
+
+        def run(x, y):
+            opt.zero_grad()
+            if is_gpt:
+                loss = net(input_ids=x, labels=x).loss
+            elif dtype == "bf16":
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    loss = torch.nn.functional.cross_entropy(net(x), y)
+            else:
+                loss = torch.nn.functional.cross_entropy(net(x), y)
+            loss.backward()
+            opt.step()
+            return loss.detach()
+
+        comm_name = "nccl (torch DDP)" if world > 1 else "none"
+        api = "pinned batch -> H2D -> stock DDP(model) forward / backward / torch.optim.SGD -> loss.item()"
+
+    pool = [to_device(h) for h in host]
+    sampler = ClockSampler(gpu_index=local_rank).start()
+    for i in range(4 + W):
+        run(*pool[i % pool_n])
+    barrier(world)
+    l0 = launches_fn()
+    mark = sampler.mark()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        loss = run(*pool[i % pool_n])
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world)
+    dev_ms = max_over_ranks(e0.elapsed_time(e1), world, dev)
+    clocks = sampler.summary(mark, sampler.mark())
+    launches = launches_fn() - l0
+    loss_val = float(loss.item())
+    # end to end: inputs come from pinned host memory every step, the loss goes back to the host every step
+    for i in range(W):
+        run(*to_device(host[i % pool_n])).item()
+    barrier(world)
+    t0 = time.perf_counter()
+    for i in range(K):
+        host_loss = run(*to_device(host[i % pool_n])).item()
+    torch.cuda.synchronize()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev)
+    sampler.stop()
+    unit_scale = T if is_gpt else 1
+    unit = "tokens/s" if is_gpt else "samples/s"
+    samples = K * B * world * unit_scale
+    emit(rank, {
+        "metric": "tokens/sec" if is_gpt else "samples/sec", "value": samples / (dev_ms / 1e3), "unit": unit, "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": dtype, "impl": args.impl,
+        "data": "synthetic " + ("token streams" if is_gpt else "ImageNet-shaped uint8 images") + ", random-init weights",
+        "config": {"model": args.model, "global_batch": B * world, "per_gpu_batch": B, "seq_len": T if is_gpt else None,
+                   "image": None if is_gpt else "3x224x224", "optimizer": "SGD lr=0.01", "parallelism": f"dp{world}",
+                   "comm": comm_name, "cuda_graph": bool(ours and not args.no_graph),
+                   "l2_policy": "model state (parameters + gradients, >= 200 MB) and activations exceed the 126 MB L2; "
+                                "inputs rotate through a pool of 8 batches"},
+        "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"), "reasons": clocks.get("reasons", []),
+                   "samples_in_region": 0 if clocks.get("pre_region_fallback") else clocks.get("samples", 0),
+                   "pre_region_fallback": bool(clocks.get("pre_region_fallback")), "source": clocks.get("source")},
+        "e2e": {"value": samples / (e2e_ms / 1e3), "unit": unit, "ms_per_step": e2e_ms / K, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 4, "api": api},
+        "gpu_launches": int(launches) if ours else 0, "final_loss": loss_val, "e2e_final_loss": host_loss,
+        "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30,
+        "repo_native_libs_loaded": loaded_native_libs(),
+    })
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     rank, local_rank, world = dist_env(args)
     quiet_stdout()
+    if args.model not in ("simplecnn", "dpp", "resnet18-cifar"):
+        try:
+            run_extra(args, rank, local_rank, world)
+        except Exception as e:
+            import traceback
+
+            traceback.print_exc()
+            emit(rank, {"impl": args.impl, "model": args.model, "unavailable": f"{type(e).__name__}: {e}"[:300]})
+        return
+    args.batch = args.batch or BATCH
     if args.impl == "reference":
         try:
             run_reference(args, rank, local_rank, world)
