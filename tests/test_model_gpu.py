@@ -143,3 +143,64 @@ def test_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+@pytest.mark.parametrize("momentum", [0.0, 0.9])
+@pytest.mark.parametrize("graph", [False, True])
+def test_optimizer_in_backward_applies_the_exact_sgd_update(momentum, graph):
+    """Per-bucket optimizer launches behind each bucket's reduction (TrainStep default) must apply exactly the update
+    optimizer.step() would: checked against torch arithmetic on the very gradients the step left in ``.grad`` (two
+    separate runs of this model are not comparable tightly: it is chaotic, see test_graph_step_matches_eager)."""
+    lr, wd = 0.05, 1e-4
+    torch.manual_seed(0)
+    model = d.DDP(d.SimpleCNN().cuda(), device_ids=[0])
+    opt = d.SGD(model.parameters(), lr=lr, momentum=momentum, weight_decay=wd)
+    step = d.TrainStep(model, d.CrossEntropyLoss(), opt, cuda_graph=graph)
+    assert step._overlap_opt
+    params = list(model.parameters())
+    g = torch.Generator(device="cpu").manual_seed(11)
+    bufs = None
+    for k in range(6 if graph else 3):        # iteration 0: one bucket; then rebuilt, tail-split units; then replays
+        old = [p.detach().clone() for p in params]
+        x = d.ops.preprocess_u8(torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).cuda())
+        loss = step(x, torch.randint(0, 10, (32,), generator=g).cuda())
+        torch.cuda.synchronize()
+        assert torch.isfinite(loss)
+        grads = [p.grad.detach() + wd * w for p, w in zip(params, old)]
+        if momentum:
+            bufs = [gr.clone() for gr in grads] if bufs is None else [momentum * b + gr for b, gr in zip(bufs, grads)]
+            upd = bufs
+        else:
+            upd = grads
+        for i, (p, w, u) in enumerate(zip(params, old, upd)):
+            assert torch.allclose(p.detach(), w - lr * u, rtol=1e-5, atol=1e-7), (k, i, float((p.detach() - (w - lr * u)).abs().max()))
+            if momentum:
+                assert torch.allclose(opt.state[p]["momentum_buffer"].view_as(u), u, rtol=1e-5, atol=1e-7), (k, i)
+    if graph:
+        assert step.replays >= 2
+
+
+def test_ragged_tail_gets_its_own_graph_on_second_sight():
+    torch.manual_seed(0)
+    model = d.DDP(d.SimpleCNN().cuda(), device_ids=[0])
+    opt = d.SGD(model.parameters(), lr=0.01)
+    step = d.TrainStep(model, d.CrossEntropyLoss(), opt, cuda_graph=True)
+
+    def run(b):
+        x = d.ops.preprocess_u8(torch.randint(0, 256, (b, 32, 32, 3), dtype=torch.uint8, device="cuda"))
+        loss = step(x, torch.randint(0, 10, (b,), device="cuda"))
+        assert torch.isfinite(loss)
+
+    for _ in range(5):
+        run(32)
+    eager0 = step.eager_steps
+    run(16)                                   # first sight of the tail shape: eager (tunes its convolutions)
+    assert step.eager_steps == eager0 + 1 and len(step._graphs) == 1
+    run(32)
+    run(16)                                   # second sight: captured
+    assert len(step._graphs) == 2 and step.eager_steps == eager0 + 1
+    run(32)
+    run(16)
+    assert step.eager_steps == eager0 + 1
+    run(8)                                    # a third shape stays eager (max_graphs = 2)
+    assert len(step._graphs) == 2
