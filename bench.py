@@ -245,13 +245,16 @@ def run_ours(args, rank, local_rank, world):
     loss_val = float(loss.item())
 
     # ---- end to end through the public API: pinned H2D + step + D2H loss, every step --------
-    ds = d.SyntheticCIFAR10(n=(K + W + 8) * B * world, seed=99)
+    ds = d.SyntheticCIFAR10(n=(2 * K + W + 8) * B * world, seed=99)
     samp = d.DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=True)
     loader = d.DeviceLoader(ds, B, samp, dev)
     it = iter(loader)
     for _ in range(W):
         x, y = next(it)
         step(x, y).item()
+    # (a) every step's loss is read back with the framework's AsyncLossReader: a pinned D2H copy right behind each
+    #     step, consumed by the host one step later, so the read-back does not drain the GPU pipeline
+    reader = d.AsyncLossReader()
     barrier(world)
     t0 = time.perf_counter()
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -259,11 +262,23 @@ def run_ours(args, rank, local_rank, world):
     host_loss = 0.0
     for _ in range(K):
         x, y = next(it)                       # pinned uint8 batch -> H2D -> fused normalise
-        host_loss = step(x, y).item()         # D2H read of the loss, every step
+        reader.push(step(x, y))               # D2H read of the loss, every step (async, pinned)
+        if reader.pending() > 1:
+            host_loss = reader.pop()
+    for v in reader.drain():
+        host_loss = v
     c1.record()
     torch.cuda.synchronize()
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max_over_ranks(max(c0.elapsed_time(c1), e2e_wall_ms), world, dev)
+    barrier(world)
+    # (b) the same loop with a blocking loss.item() per step (a full device synchronisation every step)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        x, y = next(it)
+        host_loss_blocking = step(x, y).item()
+    torch.cuda.synchronize()
+    e2e_blocking_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev)
     barrier(world)
 
     sampler.stop()
@@ -316,7 +331,10 @@ def run_ours(args, rank, local_rank, world):
         "comm_stats": log.get("comm_stats"),
         "e2e": {"value": samples / (e2e_ms / 1e3), "unit": "samples/s", "ms_per_step": e2e_ms / K,
                 "h2d_bytes_per_step": loader.h2d_bytes_per_batch, "d2h_bytes_per_step": 4,
-                "api": "DeviceLoader -> TrainStep(DDP(SimpleCNN), CrossEntropyLoss, SGD) -> loss.item()"},
+                "api": "DeviceLoader -> TrainStep(DDP(SimpleCNN), CrossEntropyLoss, SGD) -> AsyncLossReader "
+                       "(pinned D2H of every step's loss, consumed by the host one step later)",
+                "blocking_item": {"value": samples / (e2e_blocking_ms / 1e3), "ms_per_step": e2e_blocking_ms / K,
+                                  "api": "... -> loss.item() every step (device synchronisation per step)"}},
         "gpu_launches": int(launches),
         "final_loss": loss_val, "e2e_final_loss": host_loss,
         "graph_replays": step.replays, "grads_in_place": log.get("grads_produced_in_place"),
@@ -524,7 +542,7 @@ def run_extra(args, rank, local_rank, world):
         run = lambda x, y: step(x, y)
         comm_name = ddp.comm.name
         launches_fn = lambda: native.launch_count() + step.replays * native.launches_per_capture()
-        api = "pinned batch -> H2D -> TrainStep(DDP(model), loss, SGD) -> loss.item()"
+        api = "pinned batch -> H2D -> TrainStep(DDP(model), loss, SGD) -> AsyncLossReader (pinned D2H every step)"
     else:
         from torch.nn.parallel import DistributedDataParallel as StockDDP
 
@@ -563,7 +581,7 @@ def run_extra(args, rank, local_rank, world):
             return loss.detach()
 
         comm_name = "nccl (torch DDP)" if world > 1 else "none"
-        api = "pinned batch -> H2D -> stock DDP(model) forward / backward / torch.optim.SGD -> loss.item()"
+        api = "pinned batch -> H2D -> stock DDP(model) forward / backward / torch.optim.SGD -> pinned async D2H of the loss every step"
 
     pool = [to_device(h) for h in host]
     sampler = ClockSampler(gpu_index=local_rank).start()
@@ -583,13 +601,48 @@ def run_extra(args, rank, local_rank, world):
     clocks = sampler.summary(mark, sampler.mark())
     launches = launches_fn() - l0
     loss_val = float(loss.item())
-    # end to end: inputs come from pinned host memory every step, the loss goes back to the host every step
+    # end to end: inputs come from pinned host memory every step, the loss goes back to the host every step (pinned,
+    # asynchronous, consumed one step later -- the same pattern in both arms: AsyncLossReader here, a plain pinned
+    # ring for the stock stack)
+    if ours:
+        reader = d.AsyncLossReader()
+    else:
+        class _Ring:
+            def __init__(self):
+                self.buf = torch.zeros(4, dtype=torch.float32).pin_memory()
+                self.ev = [torch.cuda.Event() for _ in range(4)]
+                self.q, self.n = [], 0
+
+            def pending(self):
+                return len(self.q)
+
+            def push(self, loss):
+                s = self.n % 4
+                self.n += 1
+                self.buf[s:s + 1].copy_(loss.detach().reshape(1).float(), non_blocking=True)
+                self.ev[s].record()
+                self.q.append(s)
+
+            def pop(self):
+                s = self.q.pop(0)
+                self.ev[s].synchronize()
+                return float(self.buf[s])
+
+            def drain(self):
+                return [self.pop() for _ in range(len(self.q))]
+
+        reader = _Ring()
     for i in range(W):
         run(*to_device(host[i % pool_n])).item()
     barrier(world)
     t0 = time.perf_counter()
+    host_loss = 0.0
     for i in range(K):
-        host_loss = run(*to_device(host[i % pool_n])).item()
+        reader.push(run(*to_device(host[i % pool_n])))
+        if reader.pending() > 1:
+            host_loss = reader.pop()
+    for v in reader.drain():
+        host_loss = v
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world, dev)
     sampler.stop()

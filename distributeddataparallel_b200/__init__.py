@@ -40,6 +40,7 @@ from .train import train, CrossEntropyLoss, build_model  # noqa: E402
 from .engine import TrainStep  # noqa: E402
 from .checkpoint import save_checkpoint, load_checkpoint  # noqa: E402
 from .data import SyntheticCIFAR10, DeviceLoader, cifar10  # noqa: E402
+from .utils.loss_reader import AsyncLossReader  # noqa: E402
 
 DDP = DistributedDataParallel
 
@@ -47,5 +48,5 @@ __all__ = [
     "TrainConfig", "config_from_args", "DistributedSampler", "setup", "cleanup", "main", "spawn",
     "DistributedDataParallel", "DDP", "SGD", "Adam", "SimpleCNN", "resnet18", "resnet34", "resnet50",
     "train", "CrossEntropyLoss", "build_model", "TrainStep", "save_checkpoint", "load_checkpoint",
-    "SyntheticCIFAR10", "DeviceLoader", "cifar10", "comm_hooks",
+    "SyntheticCIFAR10", "DeviceLoader", "cifar10", "comm_hooks", "AsyncLossReader",
 ]

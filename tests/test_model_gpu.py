@@ -204,3 +204,18 @@ def test_ragged_tail_gets_its_own_graph_on_second_sight():
     assert step.eager_steps == eager0 + 1
     run(8)                                    # a third shape stays eager (max_graphs = 2)
     assert len(step._graphs) == 2
+
+
+def test_async_loss_reader_returns_every_step_loss_in_order():
+    reader = d.AsyncLossReader(depth=3)
+    vals = [torch.tensor(float(i) + 0.5, device="cuda") for i in range(7)]
+    got = []
+    for v in vals:
+        reader.push(v * 2)
+        if reader.pending() > 1:
+            got.append(reader.pop())
+    got += reader.drain()
+    assert got == [2 * (i + 0.5) for i in range(7)] and reader.pending() == 0
+    with pytest.raises(RuntimeError):
+        for v in vals:
+            reader.push(v)
