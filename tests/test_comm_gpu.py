@@ -190,3 +190,51 @@ def test_dead_peer_times_out_poisons_and_raises_error_word():
                  ctypes.c_float(0.5), ctypes.c_size_t(stage_off), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     assert (int(error[0]) & 0xFFFFFFFF) >> 16 == 0xDEAD and torch.isnan(data).all()
+
+
+def test_mixed_collectives_on_two_channels_replayed_from_a_cuda_graph():
+    """One-shot, two-shot, push and broadcast interleaved on both flag channels, captured once and replayed: epochs
+    live in device memory and only grow, so the same graph must keep working replay after replay."""
+    import ctypes
+    from distributeddataparallel_b200.ops import native
+
+    lib = native.load_library()
+    lib.b200_allreduce_push_stage_bytes.restype = ctypes.c_size_t
+    stage_bytes = lib.b200_allreduce_push_stage_bytes()
+    w = _world(4, arena_bytes=(8 << 20) + 2 * stage_bytes)
+    stage = [8 << 20, (8 << 20) + stage_bytes]
+    numel = 16384
+    offs = [0, 1 << 20, 2 << 20, 3 << 20]
+
+    def fill(it):
+        for r in range(4):
+            for k, off in enumerate(offs):
+                w.view(r, off, numel, torch.float32).fill_(float(r + 1 + k + it))
+
+    def body():
+        w.allreduce(offs[0], numel * 4, torch.float32, 1, scale=1.0, channel=0)
+        w.allreduce(offs[1], numel * 4, torch.float32, 2, scale=1.0, channel=1)
+        w.allreduce_push(offs[2], numel * 4, torch.float32, stage[0], scale=1.0, channel=0)
+        w.allreduce_push(offs[3], numel * 4, torch.float32, stage[1], scale=1.0, channel=1)
+        w.broadcast(offs[0], numel * 4, 2, channel=1)
+
+    fill(0)
+    body()                                            # warm-up (also outside capture)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    try:
+        with torch.cuda.graph(graph, stream=side):
+            body()
+    except RuntimeError as e:                         # cooperative launches not capturable on this driver
+        pytest.skip(f"cannot capture cooperative launches: {e}")
+    for it in range(1, 12):
+        fill(it)
+        torch.cuda.synchronize()
+        graph.replay()
+        torch.cuda.synchronize()
+        assert w.error_word() == 0
+        for k, off in enumerate(offs):
+            expect = float(sum(r + 1 + k + it for r in range(4)))
+            for r in range(4):
+                assert torch.all(w.view(r, off, numel, torch.float32) == expect), (it, k, r)
