@@ -684,6 +684,10 @@ def main():
 
             traceback.print_exc()
             emit(rank, {"impl": args.impl, "model": args.model, "unavailable": f"{type(e).__name__}: {e}"[:300]})
+            if world > 1:
+                sys.stdout.flush()
+                os._exit(3)          # leave at once with a failure code: the launcher then stops the peers instead of
+                                     # letting them wait in a collective for this rank
         return
     args.batch = args.batch or BATCH
     if args.impl == "reference":

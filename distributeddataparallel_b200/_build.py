@@ -83,6 +83,31 @@ def _run(cmd: List[str], log: Path) -> None:
         print(f"[build] {' '.join(cmd[:3])} ... {time.time() - t0:.1f}s", file=sys.stderr)
 
 
+class _BuildLock:
+    """Inter-process lock around a build.  When several ranks of a job find the shipped binary stale at the same time,
+    one of them builds and the others wait and then re-check: without it a rank could dlopen a half-written library
+    ("file too short") and leave its peers waiting in a collective."""
+
+    def __init__(self, name: str) -> None:
+        self.path = ROOT / "build" / f".{name}.lock"
+        self.fh = None
+
+    def __enter__(self):
+        import fcntl
+
+        self.path.parent.mkdir(parents=True, exist_ok=True)
+        self.fh = open(self.path, "w")
+        fcntl.flock(self.fh, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        import fcntl
+
+        fcntl.flock(self.fh, fcntl.LOCK_UN)
+        self.fh.close()
+        return False
+
+
 def kernel_sources() -> List[Path]:
     return sorted((CSRC / "kernels").glob("*.cu"))
 
@@ -94,6 +119,13 @@ def build_kernels(force: bool = False, verbose: bool = False) -> Path:
     digest = _digest(srcs + hdrs, " ".join(NVCC_ARCH + NVCC_FLAGS))
     if not force and not _stale(KERNEL_LIB, digest):
         return KERNEL_LIB
+    with _BuildLock("kernels"):
+        if not force and not _stale(KERNEL_LIB, digest):       # another process built it while we waited
+            return KERNEL_LIB
+        return _build_kernels_locked(srcs, hdrs, digest, force)
+
+
+def _build_kernels_locked(srcs: List[Path], hdrs: List[Path], digest: str, force: bool) -> Path:
     nvcc = _nvcc()
     if nvcc is None:
         raise RuntimeError("nvcc not found: cannot build the sm_100a kernel library")
@@ -123,8 +155,10 @@ def build_kernels(force: bool = False, verbose: bool = False) -> Path:
         for s, out in failed:
             sys.stderr.write(f"---- {s.name} ----\n{out[-6000:]}\n")
         raise RuntimeError("nvcc failed for: " + ", ".join(s.name for s, _ in failed))
-    _run([nvcc, *NVCC_ARCH, "-ccbin", "/usr/bin/g++", "-shared", "-Xcompiler", "-fPIC", "-o", str(KERNEL_LIB), *map(str, objs),
+    tmp = KERNEL_LIB.with_suffix(f".so.tmp{os.getpid()}")
+    _run([nvcc, *NVCC_ARCH, "-ccbin", "/usr/bin/g++", "-shared", "-Xcompiler", "-fPIC", "-o", str(tmp), *map(str, objs),
           "-lcudart", "-lcuda"], objdir / "link.log")
+    os.replace(tmp, KERNEL_LIB)                 # atomic: a concurrent dlopen sees the old or the new file, never half of one
     _stamp(KERNEL_LIB, digest)
     return KERNEL_LIB
 
@@ -143,6 +177,16 @@ def build_host_extension(force: bool = False) -> Path:
     digest = _digest(srcs + hdrs, " ".join(flags) + torch.__version__)
     if not force and not _stale(HOST_EXT, digest):
         return HOST_EXT
+    with _BuildLock("host"):
+        if not force and not _stale(HOST_EXT, digest):
+            return HOST_EXT
+        return _build_host_locked(srcs, hdrs, flags, digest, cxx, force)
+
+
+def _build_host_locked(srcs: List[Path], hdrs: List[Path], flags: List[str], digest: str, cxx: str, force: bool) -> Path:
+    import torch
+    from torch.utils import cpp_extension as ce
+
     inc = [f"-I{p}" for p in ce.include_paths()] + [f"-I{sysconfig.get_paths()['include']}",
                                                      f"-I{CSRC / 'reducer'}", f"-I{CSRC / 'runtime'}",
                                                      "-I/usr/local/cuda/include"]
@@ -165,9 +209,11 @@ def build_host_extension(force: bool = False) -> Path:
             raise RuntimeError(f"g++ failed for {s.name}")
         _stamp(o, sd)
     torch_lib = Path(torch.__file__).parent / "lib"
-    link = [cxx, "-shared", "-o", str(HOST_EXT), *map(str, objs), f"-L{torch_lib}", "-lc10", "-ltorch_cpu",
+    tmp = HOST_EXT.with_name(HOST_EXT.name + f".tmp{os.getpid()}")
+    link = [cxx, "-shared", "-o", str(tmp), *map(str, objs), f"-L{torch_lib}", "-lc10", "-ltorch_cpu",
             "-ltorch", "-ltorch_python", "-ldl", f"-Wl,-rpath,{torch_lib}"]
     _run(link, objdir / "link.log")
+    os.replace(tmp, HOST_EXT)
     _stamp(HOST_EXT, digest)
     return HOST_EXT
 
