@@ -1,5 +1,6 @@
 // pybind surface of the native host runtime (module name: distributeddataparallel_b200._C).
 #include "reducer.h"
+#include "step_timer.h"
 #include "vmm_arena.h"
 
 namespace py = pybind11;
@@ -52,6 +53,46 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
       .def("_autograd_hook", &Reducer::autograd_hook, release())
       .def("shadow_backward", &Reducer::shadow_backward, release())
       .def("_finalize_backward", &Reducer::finalize_backward, release());
+
+  // Device-timed step statistics (csrc/runtime/step_timer.h): the logger's timer, fed with %globaltimer stamps.
+  using b200ddp::StepSummary;
+  using b200ddp::StepTimer;
+  py::class_<StepTimer, std::shared_ptr<StepTimer>>(m, "StepTimer")
+      .def(py::init<int64_t, int64_t>(), py::arg("skip_first") = 10, py::arg("sample_every") = 1)
+      .def_static("summarize",
+                  [](const std::vector<int64_t>& marks, const std::vector<int64_t>& stamps,
+                     const std::vector<int64_t>& bytes, int world) {
+                    const StepSummary s = StepTimer::summarize(marks, stamps, bytes);
+                    py::dict d;
+                    py::list units;
+                    for (const auto& u : s.units) {
+                      py::dict e;
+                      e["unit"] = u.unit;
+                      e["bytes"] = u.bytes;
+                      e["us"] = u.us();
+                      e["bus_gbs"] = u.bus_gbs(world);
+                      units.append(e);
+                    }
+                    d["units"] = units;
+                    if (s.has_marks) {
+                      d["forward_us"] = s.forward_us;
+                      d["backward_us"] = s.backward_us;
+                      d["step_us"] = s.step_us;
+                    }
+                    if (s.has_comm) {
+                      d["comm_span_us"] = s.comm_span_us;
+                      d["comm_busy_us"] = s.comm_busy_us;
+                      d["exposed_comm_us"] = s.exposed_comm_us;
+                      d["exposed_comm_pct"] = s.exposed_comm_pct;
+                    }
+                    return d;
+                  },
+                  py::arg("marks"), py::arg("stamps"), py::arg("bytes"), py::arg("world"))
+      .def("record",
+           [](StepTimer& t, const std::vector<int64_t>& marks, const std::vector<int64_t>& stamps,
+              const std::vector<int64_t>& bytes) { return t.record(StepTimer::summarize(marks, stamps, bytes)); })
+      .def("averages", &StepTimer::averages)
+      .def("samples", &StepTimer::samples);
 
   // Symmetric arena on the CUDA VMM API + NVLink multicast (csrc/runtime/vmm_arena.h).  Stages return "" or a message.
   using b200ddp::VmmArena;

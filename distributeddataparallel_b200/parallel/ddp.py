@@ -108,6 +108,7 @@ class DistributedDataParallel(nn.Module):
         self._buffers_ahead = False        # rank 0's buffers for the next forward were already broadcast
         self._timing = False               # device-timed logger marks (enable_device_timing)
         self._marks = None
+        self._step_timer = None            # C++ running averages over the steps device_timing() was called for
 
         self.world_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
@@ -327,6 +328,7 @@ class DistributedDataParallel(nn.Module):
         self._timing = bool(on) and self.device.type == "cuda"
         if self._timing and self._marks is None:
             self._marks = torch.zeros(8, dtype=torch.int64, device=self.device)
+            self._step_timer = _C.StepTimer(0, 1)
 
     def _mark(self, slot: int) -> None:
         if self._timing:
@@ -338,33 +340,20 @@ class DistributedDataParallel(nn.Module):
         """Figures of the LAST step, from device time stamps (synchronises): forward_us, backward_us, comm_span_us,
         exposed_comm_us (= last bucket reduction end - backward compute end, clamped at 0), exposed_comm_pct of the
         step, and per-launch-unit duration / bus GB/s."""
-        out: dict = {}
         comm = self._comm
         while getattr(comm, "inner", None) is not None:
             comm = comm.inner
-        times = comm.device_times() if hasattr(comm, "device_times") else {"units": []}
-        out["units"] = [{k: u[k] for k in ("unit", "bytes", "us", "bus_gbs")} for u in times["units"]]
-        if "buffer_broadcast" in times:
-            out["buffer_broadcast_us"] = times["buffer_broadcast"]["us"]
-        if self._marks is None:
-            return out
-        torch.cuda.synchronize(self.device)
-        m = self._marks.cpu().tolist()
-        f0, b0, b1, s1 = m[self.FWD_START], m[self.BWD_START], m[self.BWD_END], m[self.STEP_END]
-        if f0 and b0 >= f0:
-            out["forward_us"] = (b0 - f0) / 1e3
-        if b0 and b1 >= b0:
-            out["backward_us"] = (b1 - b0) / 1e3
-        if f0 and s1 > f0:
-            out["step_us"] = (s1 - f0) / 1e3
-        this_step = [u for u in times["units"] if b0 and u["start_ns"] >= b0 and (not s1 or s1 < b0 or u["end_ns"] <= s1 + 10_000_000)]
-        if this_step and b1:
-            first, last = min(u["start_ns"] for u in this_step), max(u["end_ns"] for u in this_step)
-            out["comm_span_us"] = (last - first) / 1e3
-            out["comm_busy_us"] = sum(u["us"] for u in this_step)
-            out["exposed_comm_us"] = max(0.0, (last - b1) / 1e3)
-            if "step_us" in out and out["step_us"] > 0:
-                out["exposed_comm_pct"] = 100.0 * out["exposed_comm_us"] / out["step_us"]
+        stamps, nbytes, bcast = comm.raw_stamps() if hasattr(comm, "raw_stamps") else ([], [], (0, 0))
+        marks = [0, 0, 0, 0]
+        if self._marks is not None:
+            torch.cuda.synchronize(self.device)
+            marks = self._marks.cpu().tolist()[:4]
+        # the arithmetic (which reductions belong to this step, span, busy, exposed) lives in the C++ timer
+        out = dict(_C.StepTimer.summarize(marks, stamps, nbytes, self.world_size))
+        if bcast[0] and bcast[1] >= bcast[0]:
+            out["buffer_broadcast_us"] = (bcast[1] - bcast[0]) / 1e3
+        if self._step_timer is not None:
+            self._step_timer.record(marks, stamps, nbytes)
         return out
 
     def forward(self, *inputs, **kwargs):
@@ -508,6 +497,8 @@ class DistributedDataParallel(nn.Module):
         stats = getattr(self._comm, "stats", None)
         if stats is not None:
             d["comm_stats"] = stats()
+        if self._step_timer is not None and self._step_timer.samples() > 0:
+            d.update(self._step_timer.averages())      # device-timed averages (forward / backward / exposed comm)
         return d
 
     @property

@@ -525,6 +525,15 @@ class P2PComm(CommBase):
         return {"bytes": nbytes, "us": round(us, 2), "bus_gbs": round(nbytes * f / (us * 1e-6) / 1e9, 1),
                 "algo": self.ALGO_NAMES[algo]}
 
+    def raw_stamps(self):
+        """(stamps, bytes, broadcast pair): the (start, end) %globaltimer pairs of every launch unit as a flat list, the
+        payload bytes per unit, and the pair of the buffer broadcast.  Synchronises."""
+        torch.cuda.synchronize(self.device)
+        st = self._stamps.cpu().tolist()
+        n = (max(self._stamp_bytes) + 1) if self._stamp_bytes else 0
+        nbytes = [self._stamp_bytes.get(i, 0) for i in range(n)]
+        return st[:2 * n], nbytes, (st[2 * self.MAX_STAMPED], st[2 * self.MAX_STAMPED + 1])
+
     def device_times(self) -> dict:
         """Device-side (start, end) of the last reduction of every launch unit and of the buffer broadcast, in ns of
         %globaltimer (written by the kernels themselves: valid under CUDA-graph replay).  Synchronises."""

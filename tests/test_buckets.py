@@ -143,3 +143,24 @@ def test_tail_split_streams_the_last_bucket_but_reports_the_stock_layout():
     model(torch.randn(2, 3, 32, 32)).sum().backward()        # hooks fire, the reducer finalises at the end of backward
     assert [c[0] for c in comm.calls] == [0, 1, 2, 3, 4] and [c[2] for c in comm.calls] == [False] * 4 + [True]
     assert red.logging_data()["num_buckets_reduced"] == 3
+
+
+def test_step_timer_turns_device_stamps_into_logger_figures():
+    """C++ timer of the device-timed logger: which reductions belong to the step, busy vs span, exposed communication."""
+    T = _C.StepTimer
+    marks = [1_000_000, 1_300_000, 1_750_000, 1_800_000]                      # fwd start, bwd start, bwd end, step end (ns)
+    stamps = [1_310_000, 1_350_000, 1_500_000, 1_580_000, 1_740_000, 1_770_000, 900_000, 950_000]
+    out = T.summarize(marks, stamps, [9_000_000, 26_000_000, 38_144, 1000], 8)
+    assert out["forward_us"] == 300.0 and out["backward_us"] == 450.0 and out["step_us"] == 800.0
+    assert [u["unit"] for u in out["units"]] == [0, 1, 2]                    # unit 3 carries a stamp older than this backward
+    assert out["comm_busy_us"] == 150.0 and out["comm_span_us"] == 460.0
+    assert out["exposed_comm_us"] == 20.0 and abs(out["exposed_comm_pct"] - 2.5) < 1e-9
+    assert abs(out["units"][1]["bus_gbs"] - 26_000_000 * 1.75 / 80_000) < 1e-6
+    # no marks (timing not enabled): per-unit figures only
+    bare = T.summarize([0, 0, 0, 0], stamps, [9_000_000, 26_000_000, 38_144, 1000], 2)
+    assert "step_us" not in bare and "exposed_comm_us" not in bare and len(bare["units"]) == 4
+    t = T(2, 2)                                                               # skip 2, then every 2nd
+    kept = [t.record(marks, stamps, [9_000_000, 26_000_000, 38_144, 1000]) for _ in range(7)]
+    assert kept == [False, False, True, False, True, False, True] and t.samples() == 3
+    avg = t.averages()
+    assert avg["avg_exposed_comm_device_time_us"] == 20.0 and abs(avg["avg_exposed_comm_pct"] - 2.5) < 1e-9
