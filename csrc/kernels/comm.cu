@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommCtx c,
 // multimem.ld_reduce on the multicast address returns the SUM over every rank's copy, computed
 // inside NVSwitch; multimem.st writes all copies at once.  Rank r handles slice r: ingress per GPU
 // drops from 2(N-1)/N*S to ~S/N*... (one reduced stream in, one broadcast stream out) and only a few
-// SMs are needed.  Requires the arena to be a multicast-bound allocation (symm_mem provider).
+// SMs are needed.  Requires the arena to be bound to an NVLink multicast object (csrc/runtime/vmm_arena.cpp).
 template <typename T> struct Multimem;
 template <> struct Multimem<float> {
   __device__ static uint4 ld_reduce(const void* p) {
