@@ -139,6 +139,7 @@ _side: Dict[int, list] = {}          # device index -> [streams]
 _side_next: Dict[int, int] = {}
 _side_dirty: Dict[int, set] = {}     # device index -> lanes with work the caller's stream has not joined yet
 _join_queued = False
+_join_task = None          # autograd graph-task id the end-of-backward join was queued for
 
 
 def set_wgrad_streams(n: int) -> None:
@@ -181,6 +182,11 @@ def join_side_streams(device=None) -> None:
     _side_dirty.pop(idx, None)
 
 
+def _graph_task_id():
+    fn = getattr(torch._C, "_current_graph_task_id", None)
+    return fn() if fn is not None else None
+
+
 def _end_of_backward_join() -> None:
     global _join_queued
     _join_queued = False
@@ -190,7 +196,7 @@ def _end_of_backward_join() -> None:
 
 def _run_on_side(dev: torch.device, tensors, fn) -> None:
     """Run ``fn()`` (kernel launches) on a side stream forked from the current one."""
-    global _lane, _join_queued
+    global _lane, _join_queued, _join_task
     lane, stream = _side_stream(dev)
     if stream is None:
         fn()
@@ -210,10 +216,11 @@ def _run_on_side(dev: torch.device, tensors, fn) -> None:
         if t is not None:
             t.record_stream(stream)
     _side_dirty.setdefault(idx, set()).add(lane)
-    if not _join_queued:
+    task = _graph_task_id()
+    if not _join_queued or task != _join_task:   # (a backward pass that raised never ran its callbacks: re-queue)
         try:
             torch.autograd.Variable._execution_engine.queue_callback(_end_of_backward_join)
-            _join_queued = True
+            _join_queued, _join_task = True, task
         except RuntimeError:
             join_side_streams(idx)       # not inside a backward pass: join right away
 

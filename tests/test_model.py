@@ -79,3 +79,17 @@ def test_ddp_stats_summary_formatting():
     assert "256000 samples/s" in text and "data plane p2p" in text
     assert "rebuilt [9461800, 26494976, 8769792]" in text and "iterations 10" in text
     assert "0.050 ms not overlapped" in text and "bus bandwidth 455 GB/s" in text
+
+
+def test_shipped_native_libraries_match_their_sources():
+    """The in-tree binaries travel to the GPU box with the snapshot; a library older than its sources would be rebuilt
+    there by every rank at once.  (Skipped before the first build.)"""
+    from distributeddataparallel_b200 import _build
+
+    if not _build.KERNEL_LIB.exists():
+        pytest.skip("kernel library not built yet")
+    srcs = _build.kernel_sources()
+    hdrs = sorted((_build.CSRC / "kernels").glob("*.cuh")) + sorted(_build.INCLUDE.glob("*.h"))
+    digest = _build._digest(srcs + hdrs, " ".join(_build.NVCC_ARCH + _build.NVCC_FLAGS))
+    assert not _build._stale(_build.KERNEL_LIB, digest), \
+        "csrc/kernels changed after the last build: run `python -m distributeddataparallel_b200._build`"
