@@ -369,6 +369,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
   __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], accum_bar, cl_ready, cl_done;
   __shared__ uint32_t tmem_base_s;
   __shared__ unsigned ticket_s;
+  __shared__ int peer_ok_s;          // fused peer reduction: 0 once a peer's partial tile failed to arrive in time
 
   pdl_launch_dependents();            // the next kernel in the stream may set up while this one runs (common.cuh)
   const int t = threadIdx.x, warp = t >> 5;
@@ -396,6 +397,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
     if (a.tma_b) tma_prefetch_desc(&map_b);
   }
   if (t == 0) {
+    peer_ok_s = 1;
     for (int s = 0; s < STAGES; ++s) {
       // arrivals per stage: the 256 gather threads (if any operand is gathered) + the TMA issuer
       mbar_init(&full_bar[s], ((a.tma_a && a.tma_b) ? 0 : PRODUCERS) + ((a.tma_a || a.tma_b) ? 1 : 0));
@@ -800,11 +802,13 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
           while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
             if (++spins > kWaitLimit) {
               if (a.error) atomicExch(a.error, 0xBAD0FEEDu);
+              peer_ok_s = 0;                                    // the tile is marked below instead of summed from stale data
               break;
             }
           }
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
+        const bool peers_ok = peer_ok_s != 0;
         const float* mine = pr.stage[pr.rank] + (size_t)tile_id * (BM * BN);
         const size_t src_stride = (size_t)tiles * (BM * BN);
         for (int idx = t; idx < BM * BN; idx += PRODUCERS) {
@@ -812,7 +816,7 @@ __global__ void __launch_bounds__(THREADS, 1) gemm_kernel(const Args a, const __
           float v = 0.f;
           for (int p = 0; p < pr.world; ++p)                    // fixed rank order
             v += (p == pr.rank) ? stage[r * LDS + c] : __ldcg(mine + p * src_stride + (size_t)c * BM + r);
-          stage[r * LDS + c] = v * pr.scale;
+          stage[r * LDS + c] = peers_ok ? v * pr.scale : __int_as_float(0x7fc00000);
         }
         asm volatile("bar.sync 1, 256;" ::: "memory");
         // finished tile -> every rank's output, 128-byte row segments

@@ -286,6 +286,15 @@ class DistributedDataParallel(nn.Module):
             if check is not None:
                 check(sync=sync)
             comm = getattr(comm, "inner", None)
+        if sync and self.device.type == "cuda":
+            # the tcgen05 kernels' own wait-timeout word (pipeline barriers, split-K tickets): device memory, so it is
+            # read only at the synchronising call sites (log interval with sync, checkpoints, clean-up)
+            from ..ops import native
+
+            w = native.tc_error_word(self.device)
+            if w:
+                raise RuntimeError(f"a tensor-core kernel on rank {self.rank} gave up waiting inside its pipeline "
+                                   f"(error word {w:#x}): results of this step are not trustworthy")
 
     def _rebuild_buckets(self) -> None:
         order = torch.tensor(self.reducer.rebuild_order(), dtype=torch.int64)
