@@ -64,6 +64,7 @@ class DistributedDataParallel(nn.Module):
         comm: str | CommBase = "auto",
         first_bucket_mb: float = 1.0,
         allreduce_algo: str = "auto",
+        tail_splits: Optional[Sequence[int]] = None,
     ) -> None:
         super().__init__()
         named = [(n, p) for n, p in self._named_params(module)]
@@ -137,11 +138,15 @@ class DistributedDataParallel(nn.Module):
         self.reducer.set_backward_end_callback(lambda: me() is not None and me()._mark(2))
         if os.environ.get("B200DDP_DEVICE_TIMING", "0") != "0":
             self.enable_device_timing()
-        if self._comm.name == "p2p" and self.world_size > 1:
+        if tail_splits is None and self._comm.name == "p2p" and self.world_size > 1:
             # stream the last bucket (the one whose final gradient is the stem's weight gradient): pieces are
-            # reduced as they become ready, the last few KB go through the single-exchange push kernel
+            # reduced as they become ready, the last few KB go through a small-message kernel.  On by default on
+            # the P2P data plane (each extra collective costs ~10 us there; over NCCL / gloo it would not pay);
+            # ``tail_splits=[...]`` byte thresholds from the end of the bucket force it on any backend, ``[]`` disables.
             spec = os.environ.get("B200DDP_TAIL_SPLITS", f"{1 << 20},{64 << 10}")
-            self.reducer.set_tail_splits([int(v) for v in spec.split(",") if v.strip()])
+            tail_splits = [int(v) for v in spec.split(",") if v.strip()]
+        if tail_splits:
+            self.reducer.set_tail_splits([int(v) for v in tail_splits])
 
     # -- construction helpers --------------------------------------------------------------
     @staticmethod

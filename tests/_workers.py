@@ -35,14 +35,14 @@ class TinyNet(torch.nn.Module):
         return y
 
 
-def ddp_parity_worker(rank, ws, port, out_dir, steps, channels_last=False):
+def ddp_parity_worker(rank, ws, port, out_dir, steps, channels_last=False, tail_splits=None):
     """Our DDP vs stock DDP on the reference model: losses, grads, params, collective schedule."""
     d = _init(rank, ws, port)
     from torch.nn.parallel import DistributedDataParallel as StockDDP
 
     torch.manual_seed(100 + rank)            # different init per rank: ctor broadcast must fix it
     ours = d.SimpleCNN(channels_last=channels_last)
-    mine = d.DDP(ours, comm="c10d")
+    mine = d.DDP(ours, comm="c10d", tail_splits=tail_splits)
     stock_model = d.SimpleCNN(channels_last=False)
     d.ops.set_native(False)
     stock_model.load_state_dict(ours.state_dict())

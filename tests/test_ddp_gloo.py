@@ -43,6 +43,21 @@ def test_parity_with_stock_ddp(tmp_path, channels_last):
         assert r["keys"][0] == "module.model.conv1.weight" and r["keys"][-1] == "module.model.fc.bias"
 
 
+def test_streamed_last_bucket_keeps_parity_with_stock_ddp(tmp_path):
+    """tail_splits: the last bucket is reduced in three pieces (5 collectives per step instead of 3); gradients,
+    losses and parameters still match stock DDP and the reported layout stays the stock one."""
+    ws, steps = 2, 3
+    mp.spawn(W.ddp_parity_worker, args=(ws, _port(), str(tmp_path), steps, False, [1 << 20, 64 << 10]), nprocs=ws, join=True)
+    for rank in range(ws):
+        r = torch.load(tmp_path / f"rank{rank}.pt")
+        assert all(r["grads_identical"]) and max(r["grad_err"]) < 2e-3 and r["param_err"] < 1e-4
+        assert r["buckets"] == [1, 5, 5]
+        log = r["log"]
+        assert log["rebuilt_bucket_sizes"] == [9_461_800, 26_494_976, 8_769_792]
+        assert sum(log["launch_unit_sizes"]) == 44_726_568 and len(log["launch_unit_sizes"]) == 5
+        assert log["launch_unit_sizes"][-1] <= (64 << 10) and log["num_buckets_reduced"] == 1 + 3 * 2
+
+
 def test_ddp_features(tmp_path):
     ws = 2
     mp.spawn(W.features_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)

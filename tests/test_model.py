@@ -93,3 +93,14 @@ def test_shipped_native_libraries_match_their_sources():
     digest = _build._digest(srcs + hdrs, " ".join(_build.NVCC_ARCH + _build.NVCC_FLAGS))
     assert not _build._stale(_build.KERNEL_LIB, digest), \
         "csrc/kernels changed after the last build: run `python -m distributeddataparallel_b200._build`"
+
+
+def test_async_loss_reader_cpu_values_pass_through_in_order():
+    reader = d.AsyncLossReader()
+    out = []
+    for i in range(5):
+        reader.push(torch.tensor(float(i)))
+        if reader.pending() > 1:
+            out.append(reader.pop())
+    out += reader.drain()
+    assert out == [0.0, 1.0, 2.0, 3.0, 4.0] and reader.pending() == 0
