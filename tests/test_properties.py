@@ -58,3 +58,44 @@ def test_coalescing_plan_covers_every_tensor_once_within_the_limit(sizes, buffer
         assert len({tensors[i].dtype for i in g}) == 1                       # one dtype per message
         nbytes = sum(tensors[i].numel() * tensors[i].element_size() for i in g)
         assert len(g) == 1 or nbytes <= buffer_kb * 1024                      # only a lone oversized tensor may exceed
+
+
+class _NullComm:
+    def launch(self, index, flat, is_last):
+        return None
+
+
+@settings(max_examples=60, deadline=None)
+@given(sizes=st.lists(st.integers(1, 60_000), min_size=2, max_size=25),
+       thresholds=st.lists(st.integers(1, 400_000), min_size=1, max_size=3),
+       first_kb=st.integers(1, 256), cap_kb=st.integers(16, 1024))
+def test_tail_split_partitions_the_last_bucket_without_changing_the_reported_layout(sizes, thresholds, first_kb, cap_kb):
+    """Reducer.set_tail_splits: launch units are a partition of the parameters in bucket order; every stock bucket but
+    the last is one unit; the pieces of the last bucket are contiguous, and every cut sits where the gradients still
+    to come first fit under a threshold."""
+    params = [torch.nn.Parameter(torch.zeros(n)) for n in sizes]
+    alloc = lambda numel, dtype, device: torch.zeros(int(numel), dtype=dtype, device=device)
+    red = _C.Reducer(params, [list(range(len(params)))], _NullComm(), alloc, 1, True, False,
+                     [f"p{i}" for i in range(len(params))], first_kb * 1024, cap_kb * 1024)
+    order = list(reversed(range(len(params))))
+    plain = _C.Reducer(params, [list(range(len(params)))], _NullComm(), alloc, 1, True, False,
+                       [f"p{i}" for i in range(len(params))], first_kb * 1024, cap_kb * 1024)
+    stock = plain.rebuild_buckets(order)
+    red.set_tail_splits(thresholds)
+    assert [list(b) for b in red.rebuild_buckets(order)] == [list(b) for b in stock]      # reported layout unchanged
+    assert list(red.bucket_sizes()) == list(plain.bucket_sizes())
+    units = [list(u) for u in red.bucket_params()]
+    assert [i for u in units for i in u] == [i for b in stock for i in b]                  # a partition, same order
+    head = len(stock) - 1
+    assert units[:head] == [list(b) for b in stock[:head]]
+    tail_units = units[head:]
+    last = list(stock[-1])
+    assert [i for u in tail_units for i in u] == last and all(tail_units)
+    nbytes = lambda idxs: sum(params[i].numel() * 4 for i in idxs)
+    # every piece after the first starts where the remaining bytes first fit under some threshold
+    pos = 0
+    for u in tail_units[:-1]:
+        pos += len(u)
+        rest, rest_plus_one = nbytes(last[pos:]), nbytes(last[pos - 1:])
+        assert any(rest <= t < rest_plus_one for t in thresholds), (rest, rest_plus_one, thresholds)
+    assert sum(red.launch_unit_sizes()) == sum(plain.bucket_sizes())
