@@ -44,7 +44,10 @@ def build_model(cfg: TrainConfig) -> nn.Module:
     if name == "resnet50":
         return models.resnet50(cfg.num_classes)
     if name.startswith("gpt2"):
-        return models.gpt2(name, seq_len=cfg.seq_len)
+        # (not ``models.gpt2(...)``: importing the submodule ``models.gpt2`` rebinds that package attribute)
+        from .models.gpt2 import build_gpt2
+
+        return build_gpt2(name, seq_len=cfg.seq_len)
     raise ValueError(f"unknown model {cfg.model!r}")
 
 
@@ -101,7 +104,12 @@ def train(rank: int, world_size: int, epochs: int = 5, cfg: Optional[TrainConfig
         raise ValueError("--dtype bf16 applies to the transformer models (gpt2*); the convolutional models run fp32 "
                          "storage with TF32 tensor-core math")
     if is_lm:
-        dataset = SyntheticTokens(n=cfg.dataset_size, seq_len=cfg.seq_len, seed=1234)
+        from .models.gpt2 import CONFIGS as _GPT2_CONFIGS
+
+        gcfg = _GPT2_CONFIGS[cfg.model.lower()]
+        if cfg.seq_len > gcfg.block_size:
+            raise ValueError(f"--seq-len {cfg.seq_len} exceeds the context of {cfg.model} ({gcfg.block_size})")
+        dataset = SyntheticTokens(n=cfg.dataset_size, seq_len=cfg.seq_len, vocab=gcfg.vocab_size, seed=1234)
     elif cfg.image_size != 32:
         from .data import SyntheticCIFAR10
 

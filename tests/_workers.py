@@ -256,3 +256,16 @@ def ignore_worker(rank, ws, port, out_dir):
                 "names": mine._param_names, "will_sync": mine.will_sync_module_buffers()},
                os.path.join(out_dir, f"ign{rank}.pt"))
     d.cleanup()
+
+
+def lm_train_worker(rank, ws, port, out_dir):
+    """``--model gpt2-tiny`` through train(): token dataset, fused-loss model, DDP, SGD."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.set_num_threads(2)
+    import distributeddataparallel_b200 as d
+
+    cfg = d.TrainConfig(backend="gloo", device="cpu", model="gpt2-tiny", dataset_size=64, seq_len=32, batch_size=4,
+                        max_steps=4, log_interval=1, master_port=port, comm="c10d")
+    stats = d.train(rank, ws, epochs=1, cfg=cfg)
+    torch.save(stats, os.path.join(out_dir, f"lm{rank}.pt"))

@@ -86,6 +86,29 @@ def test_train_and_resume(tmp_path):
     assert s1["steps"] >= 7
 
 
+def test_train_language_model_flag_path(tmp_path):
+    """--model gpt2-tiny: train() feeds token batches (vocabulary of the chosen model) to the fused-loss GPT-2."""
+    ws = 2
+    mp.spawn(W.lm_train_worker, args=(ws, _port(), str(tmp_path)), nprocs=ws, join=True)
+    s0 = torch.load(tmp_path / "lm0.pt")
+    assert s0["steps"] == 4 and len(s0["loss_history"]) == 4
+    assert all(l == l and 0 < l < 20 for l in s0["loss_history"])
+    assert s0["ddp"]["world_size"] == 2 and s0["ddp"]["num_buckets_reduced"] >= 4
+
+
+def test_train_rejects_flag_combinations_it_cannot_honour():
+    import distributeddataparallel_b200 as d
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(_port())
+    with pytest.raises(ValueError, match="bf16"):
+        d.train(0, 1, 1, d.TrainConfig(backend="gloo", device="cpu", dtype="bf16", max_steps=1))
+    d.cleanup()
+    with pytest.raises(ValueError, match="seq-len"):
+        d.train(0, 1, 1, d.TrainConfig(backend="gloo", device="cpu", model="gpt2-tiny", seq_len=4096, max_steps=1))
+    d.cleanup()
+
+
 @pytest.mark.parametrize("divide_by_world", [True, False])
 def test_join_uneven_inputs_matches_stock(tmp_path, divide_by_world):
     """DDP.join(): rank 0 runs 2 iterations, rank 1 runs 5; nobody hangs, replicas end identical and equal
