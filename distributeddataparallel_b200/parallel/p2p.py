@@ -1,15 +1,17 @@
 """Symmetric arena + the P2P (NVLink) communication backend.
 
-This is the product data plane: gradient buckets, module buffers and broadcast staging live in
-a per-rank *symmetric arena* -- one ``cudaMalloc`` block whose CUDA-IPC handle every peer has
-opened, so that an object sits at the same offset in every rank's arena and each rank can
-``ld``/``st`` its peers' copies directly over NVLink 5 / NVSwitch.  The collectives are the
-kernels in ``csrc/kernels/comm.cu`` (barrier, one-shot and two-shot all-reduce fused with the
-1/world_size averaging, scatter+all-gather broadcast); there is no NCCL call on these paths.
+This is the product data plane: gradient buckets, module buffers and broadcast / push staging live in
+a per-rank *symmetric arena* -- one device block per rank that every peer has mapped (the C++ ``_C.VmmArena``:
+``cuMemCreate`` + fd exchange + NVLink multicast bind; CUDA IPC as the fallback), so that an object sits at the same
+offset in every rank's arena and each rank can ``ld``/``st`` its peers' copies directly over NVLink 5 / NVSwitch,
+or reduce / broadcast them inside the switch through the multicast mapping.  The collectives are the kernels in
+``csrc/kernels/comm.cu`` (barrier; push, one-shot, two-shot and NVLS all-reduce fused with the 1/world_size
+averaging; a 16-bit-wire form for the compress hooks; scatter+all-gather broadcast); there is no NCCL call on
+these paths.
 
 Replaces ProcessGroupNCCL on the reference's hot path (/root/reference/dpp.py:21,39; SURVEY.md
-§2.5(a) K2/K3/K4/K6, work items W2-W7).  The control plane -- exchanging the 64-byte IPC
-handles -- goes through ``torch.distributed`` (``all_gather_object``), as the north star allows.
+§2.5(a) K2/K3/K4/K6, work items W2-W7).  The control plane -- agreeing on the outcome of every set-up stage,
+naming the socket namespace -- goes through ``torch.distributed`` (``all_gather_object``), as the north star allows.
 
 ``EmulatedWorld`` runs the very same kernels with all "ranks" on one GPU in one cooperative
 launch; it exists so the collective logic can be tested on a single-GPU box.
@@ -770,12 +772,15 @@ class EmulatedWorld:
 
 
 class FusedGradReduce:
-    """Weight-gradient GEMM whose epilogue is the all-reduce.
+    """Weight-gradient GEMM whose epilogue is the all-reduce.  Two forms, both opt-in:
 
-    ``dW = average_over_ranks(dY_r^T @ X_r)`` computed by ONE tcgen05 kernel per rank: partial
-    tiles are pushed over NVLink to their owner rank, the owner sums them in rank order and pushes
-    the finished tile into every rank's copy of ``out`` (which must live in the symmetric arena,
-    e.g. a gradient-bucket slot), so the transfer of one tile overlaps the MMA of the next.
+    ``wgrad_nvls``  persistent 2-CTA tcgen05 GEMM; partial tiles go to this rank's copy of ``out``, the kernel's tail
+                    all-reduces them in the NVLink switch (multimem), tile by tile, replicas bit-identical.
+    ``wgrad``       (round 1) partial tiles are pushed over NVLink to their owner rank, the owner sums them in rank order
+                    and pushes the finished tile into every rank's copy of ``out``.
+
+    ``out`` must live in the symmetric arena (e.g. a gradient-bucket slot).  Measured on B200 both are slower than
+    GEMM + stand-alone all-reduce, so no model uses them by default.
     """
 
     BM = 128
